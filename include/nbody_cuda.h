@@ -1,0 +1,160 @@
+/*
+ * nbody_cuda.h -- C ABI of libnbody_cuda.so: the B200 (sm_100a) direct-sum N-body hot path.
+ *
+ * This is the drop-in boundary for ONE path of kalyniy/n-body-simulation: what a
+ * `SimulationAlgorithm::computeStep` implementation needs in order to run
+ * `NaiveSimulation` / `MpiNaiveSimulation`'s force accumulation + semi-implicit Euler update
+ * on the GPU.  Plain pointers and sizes only; no C++ or torch types cross it.  Reference
+ * citations are relative to the reference repository root.
+ *
+ * Conventions
+ *   - every `int` function returns 0 on success and a negative NBODY_E_* code on failure; the
+ *     text of the last failure is at nbody_cuda_last_error(handle) (NULL handle: the last
+ *     failure of nbody_cuda_create on this thread).  Nothing throws, nothing calls exit().
+ *   - a handle is bound to ONE device and ONE host thread at a time (the reference calls
+ *     computeStep from exactly one thread: src/Simulation.cpp:269-271).
+ *   - `particles` is the reference's 40-byte array-of-structures record
+ *     (include/Particle.hpp:53-59: position, velocity, acceleration, mass; offsets 0/12/24/36).
+ *   - there is NO CPU fallback: without a usable CUDA device every call fails with
+ *     NBODY_E_CUDA.
+ */
+#ifndef NBODY_CUDA_H
+#define NBODY_CUDA_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nbody_cuda *nbody_cuda_t;
+
+/* error codes */
+#define NBODY_OK 0
+#define NBODY_E_INVALID (-1) /* bad argument / call order */
+#define NBODY_E_CUDA (-2)    /* a CUDA runtime call failed (message has the cudaError string) */
+#define NBODY_E_NOMEM (-3)   /* device or pinned-host allocation failed */
+#define NBODY_E_STATE (-4)   /* the handle is not configured for this call */
+
+/* arithmetic modes */
+#define NBODY_MODE_FAST 0   /* FP32, packed FFMA2 + MUFU.RSQ, blocked summation (the product)            */
+#define NBODY_MODE_STRICT 1 /* FP32, the reference's exact operation order and rounding: bit-identical */
+
+/* Size of the record this library reads and writes; equals sizeof(particle_t) = 40
+ * (include/Particle.hpp:53-59). */
+size_t nbody_cuda_particle_bytes(void);
+
+/* Library / build identification, e.g. "nbody_cuda 0.1 sm_100a". */
+const char *nbody_cuda_version(void);
+
+/* Number of visible CUDA devices (0 when none or the driver is unusable). */
+int nbody_cuda_device_count(void);
+
+/* Replaces: constructing the algorithm object (src/apps/headless_main.cpp:38-69,
+ * `std::make_unique<NaiveSimulation>()`).  `device` is a CUDA ordinal. */
+int nbody_cuda_create(nbody_cuda_t *out, int device, int mode);
+void nbody_cuda_destroy(nbody_cuda_t h);
+const char *nbody_cuda_last_error(nbody_cuda_t h);
+
+/* Declares how the particle index space is sharded.  `n_total` targets are cut into `world`
+ * contiguous slices with the reference's own rule, counts[r] = n/P + (r < n%P)
+ * (src/apps/headless_main.cpp:249-259); this handle owns slice `rank`.  Replaces the per-step
+ * MPI_Allgather of counts in src/MpiNaiveSimulation.cpp:33-35 (static here).  (Re)allocates
+ * device buffers when the sizes change.  world == 1: the whole system, as NaiveSimulation. */
+int nbody_cuda_configure(nbody_cuda_t h, size_t n_total, int rank, int world);
+
+/* Slice bookkeeping of the current configuration (any pointer may be NULL). */
+int nbody_cuda_slice(nbody_cuda_t h, size_t *begin, size_t *count, size_t *slot_begin, size_t *slot_stride);
+
+/* Host AoS -> device SoA for the LOCAL slice (count = slice count of `rank`).  Replaces the
+ * MPI_Scatterv hand-over of src/apps/headless_main.cpp:264-269.  Uploads position, velocity and
+ * mass; the incoming `acceleration` field is ignored (the generators leave it uninitialised,
+ * src/Simulation.cpp:101,161,208, and computeStep overwrites it, src/NaiveSimulation.cpp:18-19).
+ * With world > 1 the other ranks' positions must then be brought in by an exchange
+ * (nbody_cuda_positions + a collective, or nbody_cuda_exchange once peers are attached). */
+int nbody_cuda_upload_aos(nbody_cuda_t h, const void *particles, size_t count);
+
+/* Device SoA -> host AoS for the local slice: writes position, velocity, acceleration; `mass`
+ * bytes are rewritten with the values that were uploaded (never modified on the device).
+ * Replaces the per-step MPI_Gatherv of src/apps/headless_main.cpp:368-373. */
+int nbody_cuda_download_aos(nbody_cuda_t h, void *particles, size_t count);
+
+/* n_steps x { force accumulation over all n_total sources for the local targets;
+ * v += a*dt; x += v*dt }  -- src/NaiveSimulation.cpp:7-51 / src/MpiNaiveSimulation.cpp:10-141.
+ * Device-resident: no host traffic.  With world > 1 this requires attached peers
+ * (nbody_cuda_peer_attach): the integrator stores each new position into every peer's array
+ * over NVLink and a device-side flag barrier closes the step (replaces the MPI_Sendrecv ring of
+ * src/MpiNaiveSimulation.cpp:106-120).  Asynchronous w.r.t. the host; ordered on the handle's
+ * stream. */
+int nbody_cuda_step(nbody_cuda_t h, float G, float dt, float min_r2, int n_steps);
+
+/* One step WITHOUT the exchange: afterwards the "current" position array holds the new
+ * positions of the local slice only, and the caller completes it with an all-gather on
+ * nbody_cuda_stream() (NCCL through torch.distributed), in place on nbody_cuda_positions(). */
+int nbody_cuda_step_local(nbody_cuda_t h, float G, float dt, float min_r2);
+
+/* The reference call itself: computeStep(std::vector<particle_t>&, const SimParams&)
+ * (include/SimulationAlgorithm.h:18-22) for world == 1 -- upload `n` particles, one step,
+ * download, synchronous.  Tolerates a different `n` on every call and n == 0. */
+int nbody_cuda_compute_step_aos(nbody_cuda_t h, void *particles, size_t n, float G, float dt, float min_r2);
+
+/* Blocks until everything queued on the handle's stream has finished. */
+int nbody_cuda_synchronize(nbody_cuda_t h);
+
+/* Device time, in milliseconds, of the most recent nbody_cuda_step / _step_local /
+ * _compute_step_aos call (CUDA events on the handle's stream; synchronises). */
+int nbody_cuda_last_step_ms(nbody_cuda_t h, float *ms);
+
+/* Per-kernel timing of the force kernel: when enabled every force launch is bracketed by CUDA
+ * events; _force_time returns the sum over launches since the last reset, and their number. */
+int nbody_cuda_profile_force(nbody_cuda_t h, int enable);
+int nbody_cuda_force_time(nbody_cuda_t h, double *total_ms, int *launches, int reset);
+
+/* Number of kernels this library has launched on the handle since creation. */
+long long nbody_cuda_launch_count(nbody_cuda_t h);
+
+/* Energy diagnostic in FP64 (no counterpart in the reference, which has no energy code):
+ * K = sum 1/2 m v^2 over the local slice; U = -G sum_{i in slice} sum_{j>i} m_i m_j / sqrt(r^2+min_r2)
+ * over global indices, so that summing K and U over ranks gives the system totals. */
+int nbody_cuda_energy(nbody_cuda_t h, float G, float min_r2, double *kinetic, double *potential);
+
+/* --- multi-GPU plumbing (one process per GPU) -------------------------------------------- */
+
+/* The handle's CUDA stream (a cudaStream_t), for torch.cuda.ExternalStream. */
+void *nbody_cuda_stream(nbody_cuda_t h);
+
+/* Device pointer to the CURRENT global position array: float4 {x,y,z,mass} per slot,
+ * `world * slot_stride` slots; rank r's particles occupy slots [r*slot_stride, r*slot_stride+counts[r]),
+ * the rest are zero-mass padding.  Valid until the next configure. */
+void *nbody_cuda_positions(nbody_cuda_t h);
+
+/* Peer-to-peer exchange set-up.  _peer_export writes an opaque NBODY_PEER_HANDLE_BYTES token
+ * describing this handle's shared block; tokens are swapped between ranks out of band
+ * (torch.distributed.all_gather_object) and each rank attaches every other rank's token.
+ * Peers must be other processes on other GPUs of the same NVLink domain. */
+#define NBODY_PEER_HANDLE_BYTES 128
+int nbody_cuda_peer_export(nbody_cuda_t h, void *token_out);
+int nbody_cuda_peer_attach(nbody_cuda_t h, int peer_rank, const void *token);
+/* Same-process variant (one process driving several GPUs): attach another handle directly. */
+int nbody_cuda_peer_attach_local(nbody_cuda_t h, int peer_rank, nbody_cuda_t peer);
+
+/* Publishes the local slice of the CURRENT position array to every attached peer and waits for
+ * theirs (the exchange that must follow nbody_cuda_upload_aos when world > 1). */
+int nbody_cuda_exchange(nbody_cuda_t h);
+
+/* FP32 FMA-pipe micro-benchmark (no counterpart in the reference): dependency-free FFMA chains
+ * (packed = 0) or FFMA2 chains (packed = 1) on every SM; reports achieved flop/s.  bench.py
+ * prints it beside the nominal #SM x 128 lanes x 2 x clock so the roofline denominator is a
+ * measured number. */
+int nbody_cuda_measure_fma_peak(nbody_cuda_t h, int packed, double *flops_per_second);
+
+/* --- host memory ------------------------------------------------------------------------- */
+
+/* Page-locked host buffers for callers that want asynchronous, full-rate PCIe copies. */
+int nbody_cuda_host_alloc(void **ptr, size_t bytes);
+int nbody_cuda_host_free(void *ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_CUDA_H */

@@ -1,0 +1,515 @@
+// nbody_kernels.cuh -- sm_100a kernels of the direct-sum hot path.
+//
+// Reference computation being replaced (citations relative to the reference repo):
+//   force accumulation  src/NaiveSimulation.cpp:12-41, src/MpiNaiveSimulation.cpp:15-125
+//   integrator          src/NaiveSimulation.cpp:43-51, src/MpiNaiveSimulation.cpp:127-141
+//   AoS record          include/Particle.hpp:53-59
+//
+// Data layout in HBM:
+//   pos[2][n_slots]  float4 {x, y, z, mass}   global, double-buffered, every rank holds all slots
+//   vel[n_local]     float4 {vx, vy, vz, -}   local slice
+//   acc[n_local]     float4 {ax, ay, az, -}   local slice
+//   partial[(grid + n_itiles) * TI] float4     scratch of the fast force kernel
+// Slot s = r * slot_stride + l holds local particle l of rank r; slots past a rank's count are
+// zero-mass padding parked far away, so they contribute exactly 0 to every sum.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace nbody {
+
+constexpr int kThreads = 256;      // threads per CTA, all kernels
+constexpr int kTileJ = 256;        // source slots per shared-memory tile (= kThreads: one load per thread)
+constexpr int kSlotAlign = 256;    // slot_stride granularity (= kTileJ, so slices start on tile edges)
+constexpr float kPadCoord = 1.0e18f;  // padding slots sit at (kPadCoord, kPadCoord, kPadCoord), mass 0
+constexpr int kMaxWorld = 16;
+
+typedef unsigned long long u64;
+
+// ---------------------------------------------------------------------------------------------
+// packed FP32x2 arithmetic (sm_100: FADD2 / FMUL2 / FFMA2) and the approximate rsqrt (MUFU.RSQ)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+    u64 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(u64 v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) {
+    u64 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) {
+    u64 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+    u64 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ float rsqrt_approx(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Work plan of the fast force kernel.
+//
+// The (target tile x source tile) rectangle is flattened into U = n_itiles * n_jtiles units;
+// CTA c of a persistent grid of G CTAs takes units [c*U/G, (c+1)*U/G): a run of consecutive
+// source tiles of one target tile, possibly continuing into the next target tile.  Every run
+// ("segment") leaves one partial sum per target in scratch slot (c + t); the finishing kernel
+// adds the segments of a target tile in ascending c, so the result does not depend on timing.
+// ---------------------------------------------------------------------------------------------
+struct ForcePlan {
+    long long units;   // U
+    int n_itiles;      // ceil(n_local / TI)
+    int n_jtiles;      // n_slots / kTileJ
+    int grid;          // G  (<= U, so no CTA is empty)
+};
+
+__host__ __device__ __forceinline__ long long plan_first_unit(const ForcePlan &p, int c) {
+    return (long long)c * p.units / p.grid;
+}
+// CTA that owns unit u: the largest c with floor(c*U/G) <= u.
+__host__ __device__ __forceinline__ int plan_owner(const ForcePlan &p, long long u) {
+    return (int)(((u + 1) * p.grid + p.units - 1) / p.units) - 1;
+}
+
+// One source tile against the I targets of this thread, packed two sources per instruction.
+// smem tile layout: A[q] = {x[2q], x[2q+1], y[2q], y[2q+1]},  B[q] = {z[2q], z[2q+1], m[2q], m[2q+1]}.
+// Per source pair and target: 3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 3 FMUL2 + 3 FFMA2.
+template <int I, bool kMaskSelf>
+__device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, const float4 *__restrict__ sB,
+                                              const u64 (&xi)[I], const u64 (&yi)[I], const u64 (&zi)[I],
+                                              u64 eps2, u64 (&ax)[I], u64 (&ay)[I], u64 (&az)[I],
+                                              int tile_slot0, const int (&self_slot)[I]) {
+#pragma unroll 4
+    for (int q = 0; q < kTileJ / 2; ++q) {
+        const float4 a = sA[q];
+        const float4 b = sB[q];
+        const u64 xj = pack2(a.x, a.y), yj = pack2(a.z, a.w), zj = pack2(b.x, b.y), mj = pack2(b.z, b.w);
+#pragma unroll
+        for (int k = 0; k < I; ++k) {
+            const u64 dx = sub2(xj, xi[k]), dy = sub2(yj, yi[k]), dz = sub2(zj, zi[k]);
+            u64 r2 = fma2(dx, dx, eps2);
+            r2 = fma2(dy, dy, r2);
+            r2 = fma2(dz, dz, r2);
+            float r2lo, r2hi;
+            unpack2(r2, r2lo, r2hi);
+            const u64 rinv = pack2(rsqrt_approx(r2lo), rsqrt_approx(r2hi));
+            const u64 rinv2 = mul2(rinv, rinv);
+            u64 s = mul2(mul2(mj, rinv), rinv2);   // m_j / r^3
+            if (kMaskSelf) {                       // the reference skips j == i by index
+                float slo, shi;
+                unpack2(s, slo, shi);
+                const int j0 = tile_slot0 + 2 * q;
+                slo = (j0 == self_slot[k]) ? 0.0f : slo;
+                shi = (j0 + 1 == self_slot[k]) ? 0.0f : shi;
+                s = pack2(slo, shi);
+            }
+            ax[k] = fma2(dx, s, ax[k]);
+            ay[k] = fma2(dy, s, ay[k]);
+            az[k] = fma2(dz, s, az[k]);
+        }
+    }
+}
+
+struct ForceArgs {
+    const float4 *pos;     // current global positions, n_slots
+    float4 *partial;       // scratch, (grid + n_itiles) * TI
+    int n_local;           // targets owned by this rank
+    int i_slot_begin;      // slot of local target 0 (multiple of kSlotAlign)
+    float eps2;            // SimParams::min_r2
+    ForcePlan plan;
+};
+
+// Fast force kernel: persistent CTAs, I targets per thread in registers, source tiles staged
+// through double-buffered shared memory in the packed-pair layout, blocked summation (one
+// inner accumulator pair per tile, flushed into an outer FP32 sum per tile).
+template <int I>
+__global__ void __launch_bounds__(kThreads, 2) force_fast_kernel(const ForceArgs a) {
+    constexpr int TI = kThreads * I;
+    __shared__ float4 sA[2][kTileJ / 2];
+    __shared__ float4 sB[2][kTileJ / 2];
+
+    const int tid = threadIdx.x;
+    const int c = blockIdx.x;
+    long long u = plan_first_unit(a.plan, c);
+    const long long u_end = plan_first_unit(a.plan, c + 1);
+    const u64 eps2 = pack2(a.eps2, a.eps2);
+
+    // where this thread parks its source particle inside a packed tile
+    float *const stA0 = reinterpret_cast<float *>(&sA[0][tid >> 1]) + (tid & 1);
+    float *const stB0 = reinterpret_cast<float *>(&sB[0][tid >> 1]) + (tid & 1);
+    constexpr int kBufFloats = (kTileJ / 2) * 4;
+
+    while (u < u_end) {
+        const int t = (int)(u / a.plan.n_jtiles);
+        const int jt0 = (int)(u - (long long)t * a.plan.n_jtiles);
+        const long long left = u_end - u;
+        const int jt1 = (a.plan.n_jtiles - jt0 < left) ? a.plan.n_jtiles : jt0 + (int)left;
+        u += jt1 - jt0;
+
+        const int islot0 = a.i_slot_begin + t * TI;        // first target slot of this tile
+        u64 xi[I], yi[I], zi[I];
+        int self_slot[I];
+#pragma unroll
+        for (int k = 0; k < I; ++k) {
+            const int l = t * TI + k * kThreads + tid;      // local target index
+            const int slot = (l < a.n_local) ? islot0 + k * kThreads + tid : islot0;
+            const float4 p = a.pos[slot];
+            xi[k] = pack2(p.x, p.x);
+            yi[k] = pack2(p.y, p.y);
+            zi[k] = pack2(p.z, p.z);
+            self_slot[k] = islot0 + k * kThreads + tid;
+        }
+        float sx[I], sy[I], sz[I];
+#pragma unroll
+        for (int k = 0; k < I; ++k) sx[k] = sy[k] = sz[k] = 0.0f;
+
+        const int diag0 = islot0 / kTileJ;                  // source tiles [diag0, diag0+I) hold the targets
+        int buf = 0;
+        {
+            const float4 p = a.pos[jt0 * kTileJ + tid];
+            stA0[0] = p.x; stA0[2] = p.y; stB0[0] = p.z; stB0[2] = p.w;
+        }
+        __syncthreads();
+        for (int jt = jt0; jt < jt1; ++jt) {
+            float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+            const bool more = (jt + 1 < jt1);
+            if (more) nxt = a.pos[(jt + 1) * kTileJ + tid];
+
+            u64 ax[I], ay[I], az[I];
+#pragma unroll
+            for (int k = 0; k < I; ++k) ax[k] = ay[k] = az[k] = 0ull;
+            if (jt >= diag0 && jt < diag0 + I)
+                tile_interact<I, true>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot);
+            else
+                tile_interact<I, false>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot);
+#pragma unroll
+            for (int k = 0; k < I; ++k) {
+                float lo, hi;
+                unpack2(ax[k], lo, hi); sx[k] += lo + hi;
+                unpack2(ay[k], lo, hi); sy[k] += lo + hi;
+                unpack2(az[k], lo, hi); sz[k] += lo + hi;
+            }
+            if (more) {
+                float *dA = stA0 + (buf ^ 1) * kBufFloats, *dB = stB0 + (buf ^ 1) * kBufFloats;
+                dA[0] = nxt.x; dA[2] = nxt.y; dB[0] = nxt.z; dB[2] = nxt.w;
+            }
+            __syncthreads();
+            buf ^= 1;
+        }
+        float4 *out = a.partial + (size_t)(c + t) * TI;
+#pragma unroll
+        for (int k = 0; k < I; ++k) out[k * kThreads + tid] = make_float4(sx[k], sy[k], sz[k], 0.0f);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Strict force kernel: the reference's exact operation order and rounding.
+// One thread per target, sources in ascending global index, j == i skipped by index,
+// every operation a separately rounded IEEE binary32 op (no FMA contraction):
+//   r = p_j - p_i; r2 = ((rx*rx + ry*ry) + rz*rz) + eps2; inv_r = 1/sqrt(r2);
+//   inv_r3 = (inv_r*inv_r)*inv_r; c = G*inv_r3; acc += (r*c)*m_j
+// (src/NaiveSimulation.cpp:28-38).  Bit-identical to NaiveSimulation by SURVEY.md F8.
+// ---------------------------------------------------------------------------------------------
+struct StrictArgs {
+    const float4 *pos;
+    float4 *acc;        // n_local
+    int n_local;
+    int i_slot_begin;
+    int world;
+    int slot_stride;
+    int counts[kMaxWorld];   // valid slots per rank
+    float G, eps2;
+};
+
+__global__ void __launch_bounds__(kThreads) force_strict_kernel(const StrictArgs a) {
+    __shared__ float4 tile[kTileJ];
+    const int tid = threadIdx.x;
+    const int l = blockIdx.x * kThreads + tid;
+    const bool live = l < a.n_local;
+    const int my_slot = a.i_slot_begin + (live ? l : 0);
+    const float4 pi = a.pos[my_slot];
+    float ax = 0.0f, ay = 0.0f, az = 0.0f;
+    for (int r = 0; r < a.world; ++r) {
+        const int base = r * a.slot_stride;
+        const int cnt = a.counts[r];
+        for (int j0 = 0; j0 < cnt; j0 += kTileJ) {
+            __syncthreads();
+            tile[tid] = a.pos[base + j0 + tid];     // slots up to slot_stride always exist
+            __syncthreads();
+            const int m = (cnt - j0 < kTileJ) ? cnt - j0 : kTileJ;
+            for (int jj = 0; jj < m; ++jj) {
+                if (base + j0 + jj == my_slot) continue;
+                const float4 pj = tile[jj];
+                const float rx = __fsub_rn(pj.x, pi.x), ry = __fsub_rn(pj.y, pi.y), rz = __fsub_rn(pj.z, pi.z);
+                const float r2 = __fadd_rn(
+                    __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz)), a.eps2);
+                const float inv_r = __fdiv_rn(1.0f, __fsqrt_rn(r2));
+                const float inv_r3 = __fmul_rn(__fmul_rn(inv_r, inv_r), inv_r);
+                const float cc = __fmul_rn(a.G, inv_r3);
+                ax = __fadd_rn(ax, __fmul_rn(__fmul_rn(rx, cc), pj.w));
+                ay = __fadd_rn(ay, __fmul_rn(__fmul_rn(ry, cc), pj.w));
+                az = __fadd_rn(az, __fmul_rn(__fmul_rn(rz, cc), pj.w));
+            }
+        }
+    }
+    if (live) a.acc[l] = make_float4(ax, ay, az, 0.0f);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Finishing kernel: (fast mode) add the segment partials of each target in ascending segment
+// order and scale by G; then the reference's semi-implicit Euler step, each product and sum
+// rounded separately (src/NaiveSimulation.cpp:47-50); then publish the new {x,y,z,m} to the
+// NEXT position array of this rank and of every attached peer (NVLink stores).
+// ---------------------------------------------------------------------------------------------
+struct FinishArgs {
+    const float4 *pos_cur;
+    float4 *pos_next;
+    float4 *vel;
+    float4 *acc;
+    const float4 *partial;
+    int n_local;
+    int i_slot_begin;
+    int TI;
+    float G, dt;
+    ForcePlan plan;
+    int n_peers;
+    float4 *peer_next[kMaxWorld];
+};
+
+template <bool kFromPartials>
+__global__ void __launch_bounds__(kThreads) finish_kernel(const FinishArgs a) {
+    const int l = blockIdx.x * kThreads + threadIdx.x;
+    if (l >= a.n_local) return;
+    float4 acc;
+    if (kFromPartials) {
+        const int t = l / a.TI, r = l - t * a.TI;
+        const int c0 = plan_owner(a.plan, (long long)t * a.plan.n_jtiles);
+        const int c1 = plan_owner(a.plan, (long long)(t + 1) * a.plan.n_jtiles - 1);
+        float sx = 0.0f, sy = 0.0f, sz = 0.0f;
+        for (int c = c0; c <= c1; ++c) {
+            const float4 p = a.partial[(size_t)(c + t) * a.TI + r];
+            sx += p.x; sy += p.y; sz += p.z;
+        }
+        acc = make_float4(a.G * sx, a.G * sy, a.G * sz, 0.0f);
+        a.acc[l] = acc;
+    } else {
+        acc = a.acc[l];
+    }
+    const int slot = a.i_slot_begin + l;
+    float4 p = a.pos_cur[slot];
+    float4 v = a.vel[l];
+    v.x = __fadd_rn(v.x, __fmul_rn(acc.x, a.dt));
+    v.y = __fadd_rn(v.y, __fmul_rn(acc.y, a.dt));
+    v.z = __fadd_rn(v.z, __fmul_rn(acc.z, a.dt));
+    p.x = __fadd_rn(p.x, __fmul_rn(v.x, a.dt));
+    p.y = __fadd_rn(p.y, __fmul_rn(v.y, a.dt));
+    p.z = __fadd_rn(p.z, __fmul_rn(v.z, a.dt));
+    a.vel[l] = v;
+    a.pos_next[slot] = p;
+    for (int q = 0; q < a.n_peers; ++q) a.peer_next[q][slot] = p;
+}
+
+// Copies the local slice of a position array to the same slots of every peer (the exchange that
+// follows an upload when world > 1).
+struct PublishArgs {
+    const float4 *src;
+    int slot_begin, n;
+    int n_peers;
+    float4 *peer[kMaxWorld];
+};
+__global__ void __launch_bounds__(kThreads) publish_kernel(const PublishArgs a) {
+    const int k = blockIdx.x * kThreads + threadIdx.x;
+    if (k >= a.n) return;
+    const float4 p = a.src[a.slot_begin + k];
+    for (int q = 0; q < a.n_peers; ++q) a.peer[q][a.slot_begin + k] = p;
+}
+
+// Cross-GPU barrier: each rank raises flag[rank] = seq in every peer's flag block once its
+// stores are system-visible, then waits until every peer has raised seq in its own block.
+struct SignalArgs {
+    unsigned seq;
+    int my_rank;
+    int n_peers;
+    unsigned *peer_flags[kMaxWorld];
+};
+__global__ void signal_kernel(const SignalArgs a) {
+    const int q = threadIdx.x;
+    if (q >= a.n_peers) return;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flags[q] + a.my_rank), "r"(a.seq) : "memory");
+}
+struct WaitArgs {
+    unsigned seq;
+    int my_rank;
+    int world;
+    const unsigned *flags;   // own block
+};
+__global__ void wait_kernel(const WaitArgs a) {
+    const int r = threadIdx.x;
+    if (r >= a.world || r == a.my_rank) return;
+    unsigned v;
+    do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.flags + r) : "memory");
+        if ((int)(v - a.seq) >= 0) break;
+        __nanosleep(100);
+    } while (true);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Boundary transposes: the reference's 40-byte AoS record <-> the SoA arrays above.
+// A CTA moves 256 records through shared memory so that global traffic on the AoS side is
+// fully coalesced (2560 consecutive floats).
+// ---------------------------------------------------------------------------------------------
+constexpr int kRecFloats = 10;   // include/Particle.hpp:53-59: 3 + 3 + 3 + 1 floats
+
+__global__ void __launch_bounds__(kThreads) aos_to_soa_kernel(const float *__restrict__ aos, int n, int slot_begin,
+                                                              float4 *__restrict__ pos, float4 *__restrict__ vel,
+                                                              float4 *__restrict__ acc) {
+    __shared__ float s[kThreads * kRecFloats];
+    const int first = blockIdx.x * kThreads;
+    const int cnt = min(kThreads, n - first);
+    const float *src = aos + (size_t)first * kRecFloats;
+    for (int k = threadIdx.x; k < cnt * kRecFloats; k += kThreads) s[k] = src[k];
+    __syncthreads();
+    if (threadIdx.x < cnt) {
+        const float *r = s + threadIdx.x * kRecFloats;
+        const int l = first + threadIdx.x;
+        pos[slot_begin + l] = make_float4(r[0], r[1], r[2], r[9]);
+        vel[l] = make_float4(r[3], r[4], r[5], 0.0f);
+        acc[l] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) soa_to_aos_kernel(float *__restrict__ aos, int n, int slot_begin,
+                                                              const float4 *__restrict__ pos,
+                                                              const float4 *__restrict__ vel,
+                                                              const float4 *__restrict__ acc) {
+    __shared__ float s[kThreads * kRecFloats];
+    const int first = blockIdx.x * kThreads;
+    const int cnt = min(kThreads, n - first);
+    if (threadIdx.x < cnt) {
+        const int l = first + threadIdx.x;
+        const float4 p = pos[slot_begin + l], v = vel[l], a = acc[l];
+        float *r = s + threadIdx.x * kRecFloats;
+        r[0] = p.x; r[1] = p.y; r[2] = p.z;
+        r[3] = v.x; r[4] = v.y; r[5] = v.z;
+        r[6] = a.x; r[7] = a.y; r[8] = a.z;
+        r[9] = p.w;
+    }
+    __syncthreads();
+    float *dst = aos + (size_t)first * kRecFloats;
+    for (int k = threadIdx.x; k < cnt * kRecFloats; k += kThreads) dst[k] = s[k];
+}
+
+// Fills position slots [begin, end) with zero-mass padding.
+__global__ void pad_kernel(float4 *pos, int begin, int end) {
+    const int k = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < end) pos[k] = make_float4(kPadCoord, kPadCoord, kPadCoord, 0.0f);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Energy diagnostic, FP64 (no counterpart in the reference).  One thread per local target i;
+// potential over sources with a larger slot (slot order == global particle order; padding has
+// mass 0).  Each CTA leaves {K, U/G} in out[2*blockIdx.x .. +1]; the host adds them in order.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) energy_kernel(const float4 *__restrict__ pos, const float4 *__restrict__ vel,
+                                                          int n_local, int i_slot_begin, int n_slots, double eps2,
+                                                          double *__restrict__ out) {
+    __shared__ float4 tile[kTileJ];
+    __shared__ double redk[kThreads / 32], redu[kThreads / 32];
+    const int tid = threadIdx.x;
+    const int l = blockIdx.x * kThreads + tid;
+    const bool live = l < n_local;
+    const int my_slot = i_slot_begin + (live ? l : 0);
+    const float4 pi = pos[my_slot];
+    const double xi = pi.x, yi = pi.y, zi = pi.z;
+    double u = 0.0;
+    const int first_tile = (i_slot_begin + blockIdx.x * kThreads) / kTileJ;   // tiles below hold no j > i
+    for (int jt = first_tile; jt < n_slots / kTileJ; ++jt) {
+        __syncthreads();
+        tile[tid] = pos[jt * kTileJ + tid];
+        __syncthreads();
+        for (int jj = 0; jj < kTileJ; ++jj) {
+            const float4 pj = tile[jj];
+            const double dx = (double)pj.x - xi, dy = (double)pj.y - yi, dz = (double)pj.z - zi;
+            const double r2 = dx * dx + dy * dy + dz * dz + eps2;
+            const double term = (double)pj.w * rsqrt(r2);
+            u += (jt * kTileJ + jj > my_slot) ? term : 0.0;   // select, so a self term of inf is dropped
+        }
+    }
+    double k = 0.0;
+    if (live) {
+        const float4 v = vel[l];
+        k = 0.5 * (double)pi.w * ((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
+        u = -(double)pi.w * u;
+    } else {
+        u = 0.0;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        k += __shfl_down_sync(0xffffffffu, k, o);
+        u += __shfl_down_sync(0xffffffffu, u, o);
+    }
+    if ((tid & 31) == 0) { redk[tid >> 5] = k; redu[tid >> 5] = u; }
+    __syncthreads();
+    if (tid == 0) {
+        double K = 0.0, U = 0.0;
+        for (int w = 0; w < kThreads / 32; ++w) { K += redk[w]; U += redu[w]; }
+        out[2 * blockIdx.x] = K;
+        out[2 * blockIdx.x + 1] = U;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// FMA-pipe micro-benchmark: dependent-free FFMA (scalar) or FFMA2 (packed) chains, used by
+// bench.py to state the measured FP32 peak next to the nominal #SM x 128 x 2 x f.
+// ---------------------------------------------------------------------------------------------
+template <bool kPacked>
+__global__ void __launch_bounds__(kThreads) fma_peak_kernel(float *out, int iters, float seed) {
+    if (kPacked) {
+        u64 acc[8];
+        // operands derived from threadIdx so they live in registers, not in the constant bank
+        const float off = (float)(threadIdx.x >> 16);
+        const u64 m = pack2(seed + off, seed * 0.5f + off), b = pack2(1e-3f + off, 2e-3f + off);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = pack2((float)threadIdx.x + k, (float)k);
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] = fma2(acc[k], m, b);
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { float lo, hi; unpack2(acc[k], lo, hi); s += lo + hi; }
+        if (s == 123.456f) out[0] = s;
+    } else {
+        float acc[16];
+        const float off = (float)(threadIdx.x >> 16);
+        const float m = seed + off, b = 1e-3f + off;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) acc[k] = (float)threadIdx.x + k;
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int k = 0; k < 16; ++k) acc[k] = fmaf(acc[k], m, b);
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) s += acc[k];
+        if (s == 123.456f) out[0] = s;
+    }
+}
+
+}  // namespace nbody

@@ -1,0 +1,297 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes -> libnbody_cuda.so), against
+the oracle and the committed golden vectors of the reference.
+
+Bars:
+  strict mode : BIT-EXACT with the reference's NaiveSimulation -- positions, velocities,
+                accelerations -- on every input and step count tested.
+  fast mode   : FP32 with a different summation order and MUFU.RSQ; single-step acceleration error
+                against the FP64 truth no larger than the reference's own FP32 error against that
+                truth (max within 1.5x to allow for a different worst particle, median no larger),
+                and within 2e-5 relative of the reference's FP32 result in the median.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_CASES, load_golden, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def same_bits(a, b):
+    return a.tobytes() == b.tobytes()
+
+
+def fields_equal(a, b):
+    return {k: same_bits(np.ascontiguousarray(a[k]), np.ascontiguousarray(b[k]))
+            for k in ("position", "velocity", "acceleration", "mass")}
+
+
+@pytest.fixture(scope="module")
+def strict(nb):
+    s = nb.CudaNaiveSimulation(mode="strict")
+    yield s
+    s.close()
+
+
+@pytest.fixture(scope="module")
+def fast(nb):
+    s = nb.CudaNaiveSimulation(mode="fast")
+    yield s
+    s.close()
+
+
+def run_compute_steps(sim, nb, p, G, dt, eps2, steps):
+    q = p.copy()
+    params = nb.SimParams(G=G, dt=dt, min_r2=eps2)
+    for _ in range(steps):
+        sim.computeStep(q, params)
+    return q
+
+
+# ------------------------------------------------------------------------------------------------
+# strict mode: bit parity
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+def test_strict_matches_reference_golden_bitwise(strict, nb, case):
+    g = load_golden(case)
+    for k in [k for k in g if k.startswith("naive_step")]:
+        steps = int(k[len("naive_step"):])
+        got = run_compute_steps(strict, nb, g["initial"], float(g["G"]), float(g["dt"]), float(g["min_r2"]), steps)
+        assert all(fields_equal(got, g[k]).values()), (case, k, fields_equal(got, g[k]))
+
+
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+def test_strict_device_resident_equals_per_step_round_trips(strict, nb, case):
+    g = load_golden(case)
+    k = sorted([k for k in g if k.startswith("naive_step")], key=lambda s: int(s[10:]))[-1]
+    steps = int(k[len("naive_step"):])
+    q = g["initial"].copy()
+    strict.upload(q)
+    strict.step(nb.SimParams(float(g["G"]), float(g["dt"]), float(g["min_r2"])), steps)
+    strict.download(q)
+    assert same_bits(q, g[k])
+
+
+def test_strict_config1_disk_4096_100_steps(strict, nb, oracle):
+    """BASELINE configs[0] trajectory: N=4096 galaxy disk (reference generator, seed 12345 when the
+    reference build is present, else this repo's generator), 100 steps, bit for bit."""
+    from oracle import Reference
+
+    if Reference.available():
+        p, eps = Reference().disk(4096, 12345)
+    else:
+        p, eps = nb.datasets.galaxy_disk(4096, seed=12345)
+    want = oracle.step_rows(p, 1.0, 0.5, eps, 100)
+    q = p.copy()
+    strict.upload(q)
+    strict.step(nb.SimParams(1.0, 0.5, eps), 100)
+    strict.download(q)
+    assert all(fields_equal(q, want).values()), fields_equal(q, want)
+
+
+@pytest.mark.parametrize("kind", ["plummer", "disk"])
+def test_strict_config2_n65536_three_steps(strict, nb, oracle, kind):
+    """BASELINE configs[1] size: bit parity at N=65536 (3 steps; the oracle needs ~1.3e10 pair terms)."""
+    if kind == "plummer":
+        p, eps = nb.datasets.plummer_sphere(65536, seed=12345)
+    else:
+        p, eps = nb.datasets.galaxy_disk(65536, seed=12345)
+    want = oracle.step_rows(p, 1.0, 0.5, eps, 3)
+    q = p.copy()
+    strict.upload(q)
+    strict.step(nb.SimParams(1.0, 0.5, eps), 3)
+    strict.download(q)
+    assert all(fields_equal(q, want).values()), fields_equal(q, want)
+
+
+# ------------------------------------------------------------------------------------------------
+# edge cases the reference's interface allows (any size, size 0, size changing per call)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ["strict", "fast"])
+@pytest.mark.parametrize("n", [0, 1, 2, 3, 31, 255, 256, 257, 511, 513, 1000, 1025, 2049])
+def test_sizes_around_tile_edges(nb, oracle, strict, fast, mode, n):
+    sim = strict if mode == "strict" else fast
+    p, eps = nb.datasets.plummer_sphere(max(n, 1), seed=n + 1)
+    p = p[:n].copy()
+    p["mass"] = np.linspace(0.5, 2.0, n, dtype=np.float32) if n else p["mass"]
+    want = oracle.step_rows(p, 1.3, 0.25, eps, 1)
+    got = run_compute_steps(sim, nb, p, 1.3, 0.25, eps, 1)
+    assert got.shape == p.shape and same_bits(np.ascontiguousarray(got["mass"]), np.ascontiguousarray(p["mass"]))
+    if mode == "strict":
+        assert same_bits(got, want)
+    elif n > 1:
+        assert rel_err(got["acceleration"], want["acceleration"]).max() < 2e-5
+        assert rel_err(got["position"], want["position"]).max() < 1e-6
+
+
+def test_size_changes_between_calls(nb, oracle, strict):
+    """computeStep must tolerate a different size() on every call (headless_main.cpp:262)."""
+    for n in (700, 64, 3000, 0, 700):
+        p, eps = nb.datasets.galaxy_disk(max(n, 2), seed=n)
+        p = p[:n].copy()
+        want = oracle.step_rows(p, 1.0, 0.5, eps, 1)
+        assert same_bits(run_compute_steps(strict, nb, p, 1.0, 0.5, eps, 1), want)
+
+
+@pytest.mark.parametrize("mode", ["strict", "fast"])
+def test_zero_mass_particles_and_zero_softening(nb, oracle, strict, fast, mode):
+    sim = strict if mode == "strict" else fast
+    p, _ = nb.datasets.plummer_sphere(777, seed=5)
+    p["mass"][::3] = 0.0                     # massless tracers feel forces but exert none
+    want = oracle.step_rows(p, 1.0, 0.5, 0.0, 1)      # min_r2 = 0: self term must be skipped by index
+    got = run_compute_steps(sim, nb, p, 1.0, 0.5, 0.0, 1)
+    assert np.isfinite(got["acceleration"]).all()
+    if mode == "strict":
+        assert same_bits(got, want)
+    else:
+        assert rel_err(got["acceleration"], want["acceleration"]).max() < 2e-5
+
+
+def test_tiny_default_softening(nb, oracle, fast):
+    """SimParams default min_r2 = 1e-8 (SimulationAlgorithm.h:8): the self term must not poison the sum."""
+    p, _ = nb.datasets.plummer_sphere(1024, seed=8)
+    want = oracle.step_rows(p, 1.0, 0.05, 1e-8, 1)
+    got = run_compute_steps(fast, nb, p, 1.0, 0.05, 1e-8, 1)
+    assert np.isfinite(got["acceleration"]).all()
+    assert rel_err(got["acceleration"], want["acceleration"]).max() < 2e-5
+
+
+def test_upload_download_round_trip(nb, fast):
+    p, _ = nb.datasets.galaxy_disk(3001, seed=3)
+    p["acceleration"] = 123.0                 # must be ignored on upload, zero before the first step
+    q = p.copy()
+    fast.upload(q)
+    out = np.zeros_like(q)
+    fast.download(out)
+    for k in ("position", "velocity", "mass"):
+        assert same_bits(np.ascontiguousarray(out[k]), np.ascontiguousarray(p[k])), k
+    assert np.all(out["acceleration"] == 0)
+
+
+def test_bad_arguments_are_reported_not_fatal(nb, fast):
+    p, _ = nb.datasets.plummer_sphere(100, seed=1)
+    fast.upload(p)
+    with pytest.raises(nb.NBodyCudaError):
+        fast.download(np.zeros(99, nb.PARTICLE_DTYPE))
+    lib = nb.load_library()
+    h = C.c_void_p()
+    assert lib.nbody_cuda_create(C.byref(h), 0, 7) == -1          # unknown mode
+    assert lib.nbody_cuda_create(C.byref(h), 4096, 0) == -1       # device out of range
+    assert b"device" in lib.nbody_cuda_last_error(None)
+
+
+# ------------------------------------------------------------------------------------------------
+# fast mode: accuracy against FP64 truth and against the reference's FP32 result
+# ------------------------------------------------------------------------------------------------
+def accuracy_report(nb, oracle, fast, p, eps):
+    truth = oracle.accel_f64(p, 1.0, eps)
+    ref32 = oracle.accel_rows(p, 1.0, eps)
+    got = run_compute_steps(fast, nb, p, 1.0, 0.5, eps, 1)
+    e_ref = rel_err(ref32, truth)
+    e_got = rel_err(got["acceleration"], truth)
+    e_vs = rel_err(got["acceleration"], ref32)
+    return dict(ref_max=e_ref.max(), ref_med=np.median(e_ref), got_max=e_got.max(), got_med=np.median(e_got),
+                vs_max=e_vs.max(), vs_med=np.median(e_vs)), got
+
+
+@pytest.mark.parametrize("kind,n", [("plummer", 4096), ("disk", 4096), ("plummer", 16384), ("disk", 16384)])
+def test_fast_accuracy_against_fp64_truth(nb, oracle, fast, kind, n):
+    p, eps = (nb.datasets.plummer_sphere if kind == "plummer" else nb.datasets.galaxy_disk)(n, seed=12345)
+    r, got = accuracy_report(nb, oracle, fast, p, eps)
+    print(kind, n, {k: float(f"{v:.3g}") for k, v in r.items()})
+    assert r["got_med"] <= r["ref_med"] * 1.05 + 1e-7      # no worse than the reference's own FP32 sum
+    assert r["got_max"] <= r["ref_max"] * 1.5 + 1e-6
+    assert r["vs_med"] <= 2e-5                             # and close to the reference's FP32 result
+    assert r["vs_max"] <= 2.0 * r["ref_max"] + 2e-6
+    # integrator: position after the step, from the same velocities
+    want = oracle.step_rows(p, 1.0, 0.5, eps, 1)
+    assert rel_err(got["position"], want["position"]).max() < 1e-5
+
+
+def test_fast_is_deterministic(nb, fast):
+    p, eps = nb.datasets.plummer_sphere(20000, seed=4)
+    a = run_compute_steps(fast, nb, p, 1.0, 0.5, eps, 2)
+    b = run_compute_steps(fast, nb, p, 1.0, 0.5, eps, 2)
+    assert same_bits(a, b)
+
+
+def test_fast_plummer_100_steps_tracks_reference(nb, oracle, fast):
+    """Multi-step parity on the non-chaotic input: N=4096 Plummer, 100 steps,
+    positions within 1e-4 of the reference trajectory (the reference's own FP32-vs-FP64 drift over
+    the same run is ~4e-6)."""
+    p, eps = nb.datasets.plummer_sphere(4096, seed=12345)
+    want = oracle.step_rows(p, 1.0, 0.5, eps, 100)
+    q = p.copy()
+    fast.upload(q)
+    fast.step(nb.SimParams(1.0, 0.5, eps), 100)
+    fast.download(q)
+    e = rel_err(q["position"], want["position"])
+    print("100-step position error max/median", e.max(), np.median(e))
+    assert e.max() < 1e-4 and np.median(e) < 1e-5
+
+
+def test_energy_matches_oracle_and_drift_parity(nb, oracle, fast):
+    p, eps = nb.datasets.plummer_sphere(4096, seed=21)
+    params = nb.SimParams(1.0, 0.5, eps)
+    fast.upload(p.copy())
+    k0, u0 = fast.energy(params)
+    ko, uo = oracle.energy(p, 1.0, eps)
+    assert k0 == pytest.approx(ko, rel=1e-10) and u0 == pytest.approx(uo, rel=1e-9)
+    fast.step(params, 20)
+    k1, u1 = fast.energy(params)
+    ref = oracle.step_rows(p, 1.0, 0.5, eps, 20)
+    kr, ur = oracle.energy(ref, 1.0, eps)
+    drift_ours = (k1 + u1 - k0 - u0) / abs(k0 + u0)
+    drift_ref = (kr + ur - ko - uo) / abs(ko + uo)
+    print("energy drift ours/ref", drift_ours, drift_ref)
+    assert drift_ours == pytest.approx(drift_ref, rel=0.01, abs=1e-7)
+
+
+# ------------------------------------------------------------------------------------------------
+# full-size, size-independent properties (BASELINE configs 2-3 sizes)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [65536, 262144])
+def test_full_size_properties(nb, oracle, fast, strict, n):
+    p, eps = nb.datasets.plummer_sphere(n, seed=12345)
+    p["mass"] = np.random.default_rng(1).uniform(0.5, 2.0, n).astype(np.float32)
+    params = nb.SimParams(1.0, 0.5, eps)
+    q = p.copy()
+    fast.upload(q)
+    fast.step(params, 1)
+    fast.download(q)
+    acc = q["acceleration"].astype(np.float64)
+    m = p["mass"].astype(np.float64)[:, None]
+    # Newton's third law as a checksum: sum m_i a_i = 0 up to rounding
+    net = np.abs((m * acc).sum(axis=0)).max()
+    scale = (m * np.abs(acc)).sum()
+    assert net / scale < 1e-6
+    # a sample of rows against the FP64 truth and the reference-order FP32 rows
+    rows = np.random.default_rng(2).choice(n, 64, replace=False)
+    for i in rows[:16]:
+        truth = oracle.accel_f64(p, 1.0, eps, int(i), int(i) + 1)
+        assert rel_err(acc[i:i + 1], truth).max() < 2e-5
+    # strict and fast agree at full size (strict is bit-equal to the reference by the tests above)
+    s = p.copy()
+    strict.upload(s)
+    strict.step(params, 1)
+    strict.download(s)
+    e = rel_err(q["acceleration"], s["acceleration"])
+    assert np.median(e) < 2e-5 and e.max() < 1e-3
+    for i in rows[:8]:
+        want = oracle.accel_rows(p, 1.0, eps, int(i), int(i) + 1)
+        assert same_bits(np.ascontiguousarray(s["acceleration"][i:i + 1]), want)
+
+
+def test_launch_counter_and_timers(nb, fast):
+    p, eps = nb.datasets.plummer_sphere(8192, seed=1)
+    fast.upload(p)
+    before = fast.launch_count()
+    fast.profile_force(True)
+    fast.step(nb.SimParams(1.0, 0.5, eps), 5)
+    ms, n = fast.force_time()
+    fast.profile_force(False)
+    assert n == 5 and ms > 0
+    assert fast.launch_count() - before == 10          # force + finish per step
+    assert fast.last_step_ms() >= ms * 0.9
