@@ -110,6 +110,11 @@ int nbody_cuda_last_step_ms(nbody_cuda_t h, float *ms);
 int nbody_cuda_profile_force(nbody_cuda_t h, int enable);
 int nbody_cuda_force_time(nbody_cuda_t h, double *total_ms, int *launches, int reset);
 
+/* Work plan of the fast force kernel for the current configuration (no counterpart in the
+ * reference): targets held per thread, persistent grid size, and the target-tile x source-tile
+ * rectangle that is cut evenly across that grid.  Any pointer may be NULL. */
+int nbody_cuda_plan(nbody_cuda_t h, int *targets_per_thread, int *grid, int *target_tiles, int *source_tiles);
+
 /* Number of kernels this library has launched on the handle since creation. */
 long long nbody_cuda_launch_count(nbody_cuda_t h);
 

@@ -58,6 +58,7 @@ SIGNATURES = {
     "nbody_cuda_last_step_ms": (_i, [_vp, C.POINTER(_f)]),
     "nbody_cuda_profile_force": (_i, [_vp, _i]),
     "nbody_cuda_force_time": (_i, [_vp, C.POINTER(_d), C.POINTER(_i), _i]),
+    "nbody_cuda_plan": (_i, [_vp, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)]),
     "nbody_cuda_launch_count": (C.c_longlong, [_vp]),
     "nbody_cuda_energy": (_i, [_vp, _f, _f, C.POINTER(_d), C.POINTER(_d)]),
     "nbody_cuda_stream": (_vp, [_vp]),

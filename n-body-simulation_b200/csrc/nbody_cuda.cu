@@ -148,34 +148,43 @@ void free_buffers(nbody_cuda_t h) {
     h->configured = false;
 }
 
-template <int I>
-int occupancy_of(int *out) {
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, force_fast_kernel<I>, kThreads, 0) == cudaSuccess ? 0 : -1;
-}
+// Targets-per-thread variants of the fast kernel and their measured relative speed (B200,
+// tools/exp/force_variants.cu): more targets per thread = fewer shared-memory reads and better
+// operand reuse, until registers run out.
+struct Variant { int I; int ctas_per_sm; double speed; };
+const Variant kVariants[] = {{1, 2, 0.80}, {2, 2, 0.90}, {4, 1, 0.95}, {6, 1, 0.99}, {7, 1, 1.00}, {8, 1, 0.97}};
 
-// Chooses the targets-per-thread variant and the persistent grid for the current sizes.
-int make_plan(nbody_cuda_t h) {
-    // fewer targets per thread when the slice is too small to give every CTA slot a target tile
-    int I = 4;
-    const size_t slots_hw = (size_t)h->sm_count * 2;
-    if (h->n_local < slots_hw * kThreads * 4 / 2) I = 2;
-    if (h->n_local < slots_hw * kThreads * 2 / 4) I = 1;
-    h->targets_per_thread = I;
-    int occ = 2;
-    int rc = (I == 4) ? occupancy_of<4>(&occ) : (I == 2) ? occupancy_of<2>(&occ) : occupancy_of<1>(&occ);
-    if (rc != 0 || occ < 1) return fail(h, NBODY_E_CUDA, "cudaOccupancyMaxActiveBlocksPerMultiprocessor failed");
-    h->force_occupancy = occ;
-    const int TI = kThreads * I;
+ForcePlan plan_for(size_t n_local, size_t n_slots, int sm_count, const Variant &v) {
+    const int TI = kThreads * v.I;
     ForcePlan p;
-    p.n_itiles = (int)((h->n_local + TI - 1) / TI);
-    p.n_jtiles = (int)(h->n_slots / kTileJ);
+    p.n_itiles = (int)((n_local + TI - 1) / TI);
+    p.n_jtiles = (int)(n_slots / kTileJ);
     p.units = (long long)p.n_itiles * p.n_jtiles;
-    long long g = (long long)h->sm_count * occ;
+    long long g = (long long)sm_count * v.ctas_per_sm;
     if (g > p.units) g = p.units;
     if (g < 1) g = 1;
     p.grid = (int)g;
-    h->plan = p;
-    const size_t need = ((size_t)p.grid + p.n_itiles) * TI;
+    return p;
+}
+
+// Chooses the variant with the smallest estimated time: the busiest SM's share of the
+// (padded) interaction rectangle divided by the variant's speed.
+int make_plan(nbody_cuda_t h) {
+    double best = 0.0;
+    int best_k = -1;
+    for (int k = 0; k < (int)(sizeof(kVariants) / sizeof(kVariants[0])); ++k) {
+        const Variant &v = kVariants[k];
+        const ForcePlan p = plan_for(h->n_local, h->n_slots, h->sm_count, v);
+        const long long per_cta = (p.units + p.grid - 1) / p.grid;                  // units of the busiest CTA
+        const int resident = (p.grid + h->sm_count - 1) / h->sm_count;              // CTAs sharing its SM
+        const double t = (double)per_cta * resident * v.I / v.speed;
+        if (best_k < 0 || t < best) { best = t; best_k = k; }
+    }
+    const Variant &v = kVariants[best_k];
+    h->targets_per_thread = v.I;
+    h->force_occupancy = v.ctas_per_sm;
+    h->plan = plan_for(h->n_local, h->n_slots, h->sm_count, v);
+    const size_t need = ((size_t)h->plan.grid + h->plan.n_itiles) * kThreads * v.I;
     if (need > h->partial_cap) {
         if (h->partial) cudaFree(h->partial);
         h->partial = nullptr; h->partial_cap = 0;
@@ -224,6 +233,9 @@ int launch_force(nbody_cuda_t h, float G, float min_r2) {
         a.n_local = (int)h->n_local; a.i_slot_begin = (int)(h->rank * h->slot_stride);
         a.eps2 = min_r2; a.plan = h->plan;
         switch (h->targets_per_thread) {
+            case 8: force_fast_kernel<8><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
+            case 7: force_fast_kernel<7><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
+            case 6: force_fast_kernel<6><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
             case 4: force_fast_kernel<4><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
             case 2: force_fast_kernel<2><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
             default: force_fast_kernel<1><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
@@ -535,6 +547,16 @@ int nbody_cuda_force_time(nbody_cuda_t h, double *total_ms, int *launches, int r
     if (total_ms) *total_ms = h->force_ms_total;
     if (launches) *launches = h->force_launches;
     if (reset) { h->force_ms_total = 0.0; h->force_launches = 0; }
+    return NBODY_OK;
+}
+
+int nbody_cuda_plan(nbody_cuda_t h, int *targets_per_thread, int *grid, int *target_tiles, int *source_tiles) {
+    if (!h) return NBODY_E_INVALID;
+    if (!h->configured) return fail(h, NBODY_E_STATE, "nbody_cuda_plan: not configured");
+    if (targets_per_thread) *targets_per_thread = h->targets_per_thread;
+    if (grid) *grid = h->plan.grid;
+    if (target_tiles) *target_tiles = h->plan.n_itiles;
+    if (source_tiles) *source_tiles = h->plan.n_jtiles;
     return NBODY_OK;
 }
 

@@ -90,7 +90,7 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
                                               const u64 (&xi)[I], const u64 (&yi)[I], const u64 (&zi)[I],
                                               u64 eps2, u64 (&ax)[I], u64 (&ay)[I], u64 (&az)[I],
                                               int tile_slot0, const int (&self_slot)[I]) {
-#pragma unroll 4
+#pragma unroll 2
     for (int q = 0; q < kTileJ / 2; ++q) {
         const float4 a = sA[q];
         const float4 b = sB[q];
@@ -133,8 +133,13 @@ struct ForceArgs {
 // Fast force kernel: persistent CTAs, I targets per thread in registers, source tiles staged
 // through double-buffered shared memory in the packed-pair layout, blocked summation (one
 // inner accumulator pair per tile, flushed into an outer FP32 sum per tile).
+// One CTA per SM for I >= 4: its eight warps stay in step through the per-tile barrier, so no
+// warp is left running alone at the end (two independent CTAs per SM drift apart), and with two
+// warps per scheduler consecutive instructions of a warp issue back to back, which keeps the
+// operand-reuse cache effective (the register file, not the FMA pipe, is the tighter resource
+// for FFMA2 with three distinct register pairs).
 template <int I>
-__global__ void __launch_bounds__(kThreads, 2) force_fast_kernel(const ForceArgs a) {
+__global__ void __launch_bounds__(kThreads, (I >= 4) ? 1 : 2) force_fast_kernel(const ForceArgs a) {
     constexpr int TI = kThreads * I;
     __shared__ float4 sA[2][kTileJ / 2];
     __shared__ float4 sB[2][kTileJ / 2];

@@ -243,6 +243,12 @@ class CudaNaiveSimulation:
         self._ck(self._lib.nbody_cuda_force_time(self._h, C.byref(ms), C.byref(n), int(reset)))
         return ms.value, n.value
 
+    def plan(self):
+        """Work plan of the fast force kernel: targets per thread, grid, target tiles, source tiles."""
+        a, b, c, d = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        self._ck(self._lib.nbody_cuda_plan(self._h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return dict(targets_per_thread=a.value, grid=b.value, target_tiles=c.value, source_tiles=d.value)
+
     def launch_count(self) -> int:
         return int(self._lib.nbody_cuda_launch_count(self._h))
 

@@ -21,6 +21,7 @@ for n in sizes:
     sim.profile_force(False)
     rate = n * n * steps / (ms * 1e-3)
     frate = n * n * fl / (fms * 1e-3)
+    print(sim.plan(), end=" ")
     print(f"fast n={n} steps={steps} {ms/steps:.3f} ms/step {rate:.3e} int/s  force-only {frate:.3e} int/s "
           f"= {frate*20/1e12:.1f} TFLOP/s(20-flop)", flush=True)
 st = nb.CudaNaiveSimulation(mode="strict")
