@@ -57,6 +57,7 @@ struct nbody_cuda {
     unsigned *flags = nullptr;
     int cur = 0;
     unsigned barrier_seq = 0;
+    unsigned long long barrier_timeout_ns = 30ull * 1000000000ull;
 
     // local state
     float4 *vel = nullptr, *acc = nullptr;
@@ -255,6 +256,19 @@ void fill_peer_ptrs(nbody_cuda_t h, int which_pos, float4 **out, int *n) {
     *n = k;
 }
 
+constexpr int kFaultWord = 32;   // flags[0..15]: barrier counters, flags[32]: barrier fault
+
+// Reports a barrier that gave up (a peer never arrived).  Called after a stream synchronise.
+int check_fault(nbody_cuda_t h) {
+    if (h->world == 1 || !h->flags) return NBODY_OK;
+    unsigned f = 0;
+    CU_TRY(h, cudaMemcpy(&f, h->flags + kFaultWord, sizeof(f), cudaMemcpyDeviceToHost));
+    if (f != 0)
+        return fail(h, NBODY_E_CUDA, "peer exchange timed out waiting for rank " + std::to_string((int)f - 1) +
+                                         " (ranks out of step, or a peer process died)");
+    return NBODY_OK;
+}
+
 unsigned *peer_flags_of(nbody_cuda_t h, int r) {
     return reinterpret_cast<unsigned *>(reinterpret_cast<float4 *>(h->peer_block[r]) + 2 * h->n_slots);
 }
@@ -272,6 +286,7 @@ int launch_barrier(nbody_cuda_t h) {
     CHECK_LAUNCH(h, "signal_kernel");
     WaitArgs w;
     w.seq = h->barrier_seq; w.my_rank = h->rank; w.world = h->world; w.flags = h->flags;
+    w.fault = h->flags + kFaultWord; w.timeout_ns = h->barrier_timeout_ns;
     wait_kernel<<<1, 32, 0, h->stream>>>(w);
     CHECK_LAUNCH(h, "wait_kernel");
     return NBODY_OK;
@@ -469,7 +484,7 @@ int nbody_cuda_download_aos(nbody_cuda_t h, void *particles, size_t count) {
     CHECK_LAUNCH(h, "soa_to_aos_kernel");
     CU_TRY(h, cudaMemcpyAsync(particles, h->d_aos, bytes, cudaMemcpyDeviceToHost, h->stream));
     CU_TRY(h, cudaStreamSynchronize(h->stream));
-    return NBODY_OK;
+    return check_fault(h);
 }
 
 int nbody_cuda_step(nbody_cuda_t h, float G, float dt, float min_r2, int n_steps) {
@@ -515,7 +530,7 @@ int nbody_cuda_synchronize(nbody_cuda_t h) {
     if (!h) return NBODY_E_INVALID;
     CU_TRY(h, cudaSetDevice(h->device));
     CU_TRY(h, cudaStreamSynchronize(h->stream));
-    return NBODY_OK;
+    return check_fault(h);
 }
 
 int nbody_cuda_last_step_ms(nbody_cuda_t h, float *ms) {

@@ -358,16 +358,25 @@ struct WaitArgs {
     unsigned seq;
     int my_rank;
     int world;
-    const unsigned *flags;   // own block
+    const unsigned *flags;   // own block: flags[r] = last barrier rank r has reached
+    unsigned *fault;         // own block: set to 1 + r if rank r never arrived
+    unsigned long long timeout_ns;
 };
 __global__ void wait_kernel(const WaitArgs a) {
     const int r = threadIdx.x;
     if (r >= a.world || r == a.my_rank) return;
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     unsigned v;
     do {
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.flags + r) : "memory");
         if ((int)(v - a.seq) >= 0) break;
-        __nanosleep(100);
+        __nanosleep(200);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > a.timeout_ns) {          // a peer died or fell out of step: give up instead of hanging the GPU
+            *a.fault = 1u + (unsigned)r;
+            break;
+        }
     } while (true);
 }
 
