@@ -153,6 +153,30 @@ int nbody_cuda_exchange(nbody_cuda_t h);
  * measured number. */
 int nbody_cuda_measure_fma_peak(nbody_cuda_t h, int packed, double *flops_per_second);
 
+/* Accelerations of n bodies on one another WITHOUT any allocation (this entry point has no
+ * counterpart in the reference).  For hosts that must keep this library away from the device
+ * allocator: an application that gave all GPU memory to its own arena at start-up, a stepping loop
+ * that cannot tolerate the device-wide synchronisation of cudaMalloc / cudaFree, a process already
+ * at its memory budget.  The call makes no cudaMalloc, cudaFree or other allocating call; its
+ * working memory is a fixed 7 MiB array built into the library image (resident on every GPU that
+ * loads the library, until exit), which is why n is limited to NBODY_NOALLOC_MAX_N -- larger n
+ * is refused with NBODY_E_INVALID and a message, nothing is launched.
+ *
+ *   d_positions      device pointer, n x float4 {x, y, z, mass}       (read)
+ *   d_accelerations  device pointer, n x float4 {ax, ay, az, 0}       (written)
+ *   stream           a cudaStream_t, or NULL for the default stream; the call only enqueues work
+ *   err, err_len     optional buffer that receives the failure text (may be NULL / 0)
+ *
+ * Same arithmetic as NBODY_MODE_FAST (a_i = G * sum_{j != i} m_j (p_j - p_i) / (r^2 + min_r2)^1.5).
+ * Runs on the CURRENT device.  The first call on each device looks up where the built-in array
+ * lives on that GPU (cudaGetSymbolAddress); make that first call before any stream capture begins.
+ * All calls share the one array and it keeps whatever the previous call left (each call rewrites
+ * everything it reads, so nothing needs clearing): calls whose kernels overlap on the same GPU
+ * -- two streams, two threads -- race; serialise them. */
+#define NBODY_NOALLOC_MAX_N 65536
+int nbody_cuda_accel_noalloc(const void *d_positions, void *d_accelerations, size_t n, float G, float min_r2,
+                             void *stream, char *err, size_t err_len);
+
 /* --- host memory ------------------------------------------------------------------------- */
 
 /* Page-locked host buffers for callers that want asynchronous, full-rate PCIe copies. */

@@ -68,6 +68,7 @@ SIGNATURES = {
     "nbody_cuda_peer_attach_local": (_i, [_vp, _i, _vp]),
     "nbody_cuda_exchange": (_i, [_vp]),
     "nbody_cuda_measure_fma_peak": (_i, [_vp, _i, C.POINTER(_d)]),
+    "nbody_cuda_accel_noalloc": (_i, [_vp, _vp, _sz, _f, _f, _vp, C.c_char_p, _sz]),
     "nbody_cuda_host_alloc": (_i, [C.POINTER(_vp), _sz]),
     "nbody_cuda_host_free": (_i, [_vp]),
 }

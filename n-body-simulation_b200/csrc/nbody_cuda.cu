@@ -734,3 +734,122 @@ int nbody_cuda_measure_fma_peak(nbody_cuda_t h, int packed, double *flops_per_se
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free accelerations.
+//
+// Who needs it: hosts that embed this library but may not let it touch the device allocator --
+// an engine that handed the whole GPU to its own arena at start-up (a later cudaMalloc can fail
+// or fragment it), a stepping loop that cannot afford the device-wide synchronisation cudaMalloc
+// and cudaFree imply, a process already at its memory budget.  Every other entry point of this
+// library grows device buffers on demand; this one never does.  Its working memory -- the
+// tile-padded copy of the sources and the segment partials of the fast force kernel -- lives in
+// the fixed array below, which every GPU that loads the library carries until the process ends.
+//
+// The array is shared by all calls and is never cleared: nothing in it has to start at zero,
+// because each call rewrites the padding of the staging area and every partial it later reads
+// before reading it.  For the same reason two calls whose kernels overlap on a GPU (different
+// streams, different threads) corrupt each other: run them one after the other.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t kNoAllocMaxN = NBODY_NOALLOC_MAX_N;                     // sources == targets
+constexpr size_t kNoAllocStageSlots = kNoAllocMaxN;                      // multiple of kTileJ
+constexpr size_t kNoAllocPartialSlots = 384 * 1024;                      // float4; >= (grid + target tiles) * 256 * I
+constexpr size_t kNoAllocSlots = kNoAllocStageSlots + kNoAllocPartialSlots;   // 458752 float4 = 7 MiB
+static_assert(kNoAllocMaxN % kTileJ == 0, "staging area must be whole tiles");
+
+static __device__ __align__(256) float4 g_noalloc_scratch[kNoAllocSlots];
+
+constexpr int kNoAllocMaxDevices = 64;
+struct NoAllocDevice {
+    bool ready = false;
+    float4 *scratch = nullptr;   // DEVICE address of g_noalloc_scratch on that GPU
+    int sm_count = 0;
+};
+NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+
+int noalloc_fail(char *err, size_t err_len, int code, const char *what, cudaError_t e = cudaSuccess) {
+    if (err && err_len) {
+        if (e != cudaSuccess) snprintf(err, err_len, "nbody_cuda_accel_noalloc: %s: %s", what, cudaGetErrorString(e));
+        else snprintf(err, err_len, "nbody_cuda_accel_noalloc: %s", what);
+    }
+    if (e != cudaSuccess) cudaGetLastError();
+    return code;
+}
+
+// Same choice as make_plan(), without a handle and without touching any buffer.
+int noalloc_pick_variant(size_t n, size_t n_slots, int sm_count, ForcePlan *plan) {
+    double best = 0.0;
+    int best_k = -1;
+    for (int k = 0; k < (int)(sizeof(kVariants) / sizeof(kVariants[0])); ++k) {
+        const ForcePlan p = plan_for(n, n_slots, sm_count, kVariants[k]);
+        const long long per_cta = (p.units + p.grid - 1) / p.grid;
+        const int resident = (p.grid + sm_count - 1) / sm_count;
+        const double t = (double)per_cta * resident * kVariants[k].I / kVariants[k].speed;
+        if (best_k < 0 || t < best) { best = t; best_k = k; }
+    }
+    *plan = plan_for(n, n_slots, sm_count, kVariants[best_k]);
+    return kVariants[best_k].I;
+}
+
+}  // namespace
+
+extern "C" int nbody_cuda_accel_noalloc(const void *d_positions, void *d_accelerations, size_t n, float G, float min_r2,
+                                        void *stream, char *err, size_t err_len) {
+    if (err && err_len) err[0] = 0;
+    if (n > kNoAllocMaxN) {
+        if (err && err_len)
+            snprintf(err, err_len, "nbody_cuda_accel_noalloc: n = %zu exceeds NBODY_NOALLOC_MAX_N = %zu (the built-in scratch "
+                     "is fixed; use nbody_cuda_step on a handle for larger systems)", n, (size_t)kNoAllocMaxN);
+        return NBODY_E_INVALID;
+    }
+    if (n == 0) return NBODY_OK;
+    if (!d_positions || !d_accelerations) return noalloc_fail(err, err_len, NBODY_E_INVALID, "positions / accelerations is NULL");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return noalloc_fail(err, err_len, NBODY_E_CUDA, "cudaGetDevice", e);
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return noalloc_fail(err, err_len, NBODY_E_INVALID, "device ordinal out of range");
+    NoAllocDevice &d = g_noalloc_dev[dev];
+    if (!d.ready) {
+        // One-time set-up on this device (it is the current one): in host code the name
+        // g_noalloc_scratch is only a stand-in for the symbol, not an address a kernel can use, so
+        // ask the runtime where the array lives on THIS GPU and hand that pointer to the kernels.
+        float4 *ptr = nullptr;
+        e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) return noalloc_fail(err, err_len, NBODY_E_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch)", e);
+        int sms = 0;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess || sms <= 0) return noalloc_fail(err, err_len, NBODY_E_CUDA, "cudaDeviceGetAttribute(multiProcessorCount)", e);
+        d.scratch = ptr;
+        d.sm_count = sms;
+        d.ready = true;
+    }
+    const size_t n_slots = (n + kTileJ - 1) / kTileJ * kTileJ;
+    ForcePlan plan;
+    const int I = noalloc_pick_variant(n, n_slots, d.sm_count, &plan);
+    const size_t need = ((size_t)plan.grid + plan.n_itiles) * kThreads * I;
+    if (need > kNoAllocPartialSlots)
+        return noalloc_fail(err, err_len, NBODY_E_INVALID, "this GPU's SM count needs more partial-sum scratch than the built-in array holds");
+    cudaStream_t st = (cudaStream_t)stream;
+    float4 *stage = d.scratch;
+    float4 *partial = d.scratch + kNoAllocStageSlots;
+
+    stage_positions_kernel<<<(int)(n_slots / kThreads), kThreads, 0, st>>>((const float4 *)d_positions, (int)n, stage, (int)n_slots);
+    if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(err, err_len, NBODY_E_CUDA, "launch of stage_positions_kernel", e);
+    ForceArgs a;
+    a.pos = stage; a.partial = partial; a.n_local = (int)n; a.i_slot_begin = 0; a.eps2 = min_r2; a.plan = plan;
+    switch (I) {
+        case 8: force_fast_kernel<8><<<plan.grid, kThreads, 0, st>>>(a); break;
+        case 7: force_fast_kernel<7><<<plan.grid, kThreads, 0, st>>>(a); break;
+        case 6: force_fast_kernel<6><<<plan.grid, kThreads, 0, st>>>(a); break;
+        case 4: force_fast_kernel<4><<<plan.grid, kThreads, 0, st>>>(a); break;
+        case 2: force_fast_kernel<2><<<plan.grid, kThreads, 0, st>>>(a); break;
+        default: force_fast_kernel<1><<<plan.grid, kThreads, 0, st>>>(a); break;
+    }
+    if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(err, err_len, NBODY_E_CUDA, "launch of force_fast_kernel", e);
+    reduce_partials_kernel<<<(int)((n + kThreads - 1) / kThreads), kThreads, 0, st>>>(partial, (int)n, kThreads * I, G, plan,
+                                                                                      (float4 *)d_accelerations);
+    if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(err, err_len, NBODY_E_CUDA, "launch of reduce_partials_kernel", e);
+    return NBODY_OK;
+}

@@ -485,6 +485,33 @@ __global__ void __launch_bounds__(kThreads) energy_kernel(const float4 *__restri
 }
 
 // ---------------------------------------------------------------------------------------------
+// Helpers of the allocation-free entry point (nbody_cuda_accel_noalloc): copy the caller's n
+// sources into a tile-padded staging area, and fold the fast kernel's segment partials into
+// accelerations.  Both only ever touch memory handed to them.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) stage_positions_kernel(const float4 *__restrict__ src, int n,
+                                                                   float4 *__restrict__ dst, int n_slots) {
+    const int k = blockIdx.x * kThreads + threadIdx.x;
+    if (k >= n_slots) return;
+    dst[k] = (k < n) ? src[k] : make_float4(kPadCoord, kPadCoord, kPadCoord, 0.0f);   // padding is rewritten every call
+}
+
+__global__ void __launch_bounds__(kThreads) reduce_partials_kernel(const float4 *__restrict__ partial, int n, int TI,
+                                                                   float G, ForcePlan plan, float4 *__restrict__ acc) {
+    const int l = blockIdx.x * kThreads + threadIdx.x;
+    if (l >= n) return;
+    const int t = l / TI, r = l - t * TI;
+    const int c0 = plan_owner(plan, (long long)t * plan.n_jtiles);
+    const int c1 = plan_owner(plan, (long long)(t + 1) * plan.n_jtiles - 1);
+    float sx = 0.0f, sy = 0.0f, sz = 0.0f;
+    for (int c = c0; c <= c1; ++c) {           // same order as finish_kernel: ascending segment
+        const float4 p = partial[(size_t)(c + t) * TI + r];
+        sx += p.x; sy += p.y; sz += p.z;
+    }
+    acc[l] = make_float4(G * sx, G * sy, G * sz, 0.0f);
+}
+
+// ---------------------------------------------------------------------------------------------
 // FMA-pipe micro-benchmark: dependent-free FFMA (scalar) or FFMA2 (packed) chains, used by
 // bench.py to state the measured FP32 peak next to the nominal #SM x 128 x 2 x f.
 // ---------------------------------------------------------------------------------------------
