@@ -56,6 +56,7 @@ struct nbody_cuda {
     float4 *pos[2] = {nullptr, nullptr};
     unsigned *flags = nullptr;
     int cur = 0;
+    bool mass_checked = false;   // mass_info (flags[40..41]) describes the uploaded masses
     unsigned barrier_seq = 0;
     unsigned long long barrier_timeout_ns = 30ull * 1000000000ull;
 
@@ -117,6 +118,10 @@ int fail(nbody_cuda_t h, int code, const std::string &msg) {
     } while (0)
 
 size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// words of the 64-word flag block that follows the position arrays
+constexpr int kFaultWord = 32;    // flags[0..15]: barrier counters, flags[32]: barrier fault
+constexpr int kMassInfoWord = 40; // flags[40]: masses differ, flags[41]: bits of the common mass
 
 void slice_of(size_t n, int world, int r, size_t *begin, size_t *count) {
     // counts[r] = n/P + (r < n%P), displs = prefix sum: src/apps/headless_main.cpp:249-259
@@ -204,6 +209,24 @@ int ensure_aos(nbody_cuda_t h, size_t bytes) {
     return NBODY_OK;
 }
 
+// Masses never change on the device, so one look after each upload (and after the exchange that
+// completes the replicated array) tells the fast kernel whether it may drop m_j from its loop.
+int ensure_mass_info(nbody_cuda_t h) {
+    if (h->mass_checked || h->mode != NBODY_MODE_FAST || h->n_total == 0) return NBODY_OK;
+    unsigned *info = h->flags + kMassInfoWord;
+    CU_TRY(h, cudaMemsetAsync(info, 0, 2 * sizeof(unsigned), h->stream));
+    MassCheckArgs a;
+    a.pos = h->pos[h->cur]; a.info = info; a.world = h->world; a.slot_stride = (int)h->slot_stride;
+    a.first_slot = 0;
+    for (int r = 0; r < kMaxWorld; ++r) a.counts[r] = h->counts[r];
+    for (int r = 0; r < h->world; ++r)
+        if (h->counts[r] > 0) { a.first_slot = (int)(r * h->slot_stride); break; }
+    mass_check_kernel<<<(int)((h->n_slots + kThreads - 1) / kThreads), kThreads, 0, h->stream>>>(a);
+    CHECK_LAUNCH(h, "mass_check_kernel");
+    h->mass_checked = true;
+    return NBODY_OK;
+}
+
 int launch_force(nbody_cuda_t h, float G, float min_r2) {
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (h->profile_force) {
@@ -233,6 +256,7 @@ int launch_force(nbody_cuda_t h, float G, float min_r2) {
         a.pos = h->pos[h->cur]; a.partial = h->partial;
         a.n_local = (int)h->n_local; a.i_slot_begin = (int)(h->rank * h->slot_stride);
         a.eps2 = min_r2; a.plan = h->plan;
+        a.mass_info = h->flags + kMassInfoWord;
         switch (h->targets_per_thread) {
             case 8: force_fast_kernel<8><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
             case 7: force_fast_kernel<7><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
@@ -256,7 +280,6 @@ void fill_peer_ptrs(nbody_cuda_t h, int which_pos, float4 **out, int *n) {
     *n = k;
 }
 
-constexpr int kFaultWord = 32;   // flags[0..15]: barrier counters, flags[32]: barrier fault
 
 // Reports a barrier that gave up (a peer never arrived).  Called after a stream synchronise.
 int check_fault(nbody_cuda_t h) {
@@ -300,6 +323,7 @@ int launch_finish(nbody_cuda_t h, float G, float dt, bool publish) {
     a.TI = kThreads * h->targets_per_thread;
     a.G = G; a.dt = dt; a.plan = h->plan;
     a.n_peers = 0;
+    a.mass_info = h->flags + kMassInfoWord;
     if (publish) fill_peer_ptrs(h, h->cur ^ 1, a.peer_next, &a.n_peers);
     const int grid = (int)((h->n_local + kThreads - 1) / kThreads);
     if (h->mode == NBODY_MODE_STRICT) finish_kernel<false><<<grid, kThreads, 0, h->stream>>>(a);
@@ -310,6 +334,7 @@ int launch_finish(nbody_cuda_t h, float G, float dt, bool publish) {
 
 int one_step(nbody_cuda_t h, float G, float dt, float min_r2, bool exchange) {
     int rc;
+    if ((rc = ensure_mass_info(h)) != NBODY_OK) return rc;
     if (h->n_local > 0) {
         if ((rc = launch_force(h, G, min_r2)) != NBODY_OK) return rc;
         if ((rc = launch_finish(h, G, dt, exchange)) != NBODY_OK) return rc;
@@ -426,6 +451,7 @@ int nbody_cuda_configure(nbody_cuda_t h, size_t n_total, int rank, int world) {
     for (int r = 0; r < world; ++r) { size_t b, c; slice_of(n_total, world, r, &b, &c); h->counts[r] = (int)c; }
     h->cur = 0;
     h->barrier_seq = 0;
+    h->mass_checked = false;
     // everything is padding until particles arrive
     const int total = (int)(2 * n_slots);
     pad_kernel<<<(total + 255) / 256, 256, 0, h->stream>>>(h->pos[0], 0, total);
@@ -465,6 +491,7 @@ int nbody_cuda_upload_aos(nbody_cuda_t h, const void *particles, size_t count) {
     aos_to_soa_kernel<<<grid, kThreads, 0, h->stream>>>(reinterpret_cast<const float *>(h->d_aos), (int)count,
                                                        (int)(h->rank * h->slot_stride), h->pos[h->cur], h->vel, h->acc);
     CHECK_LAUNCH(h, "aos_to_soa_kernel");
+    h->mass_checked = false;
     return NBODY_OK;
 }
 
@@ -839,6 +866,7 @@ extern "C" int nbody_cuda_accel_noalloc(const void *d_positions, void *d_acceler
     if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(err, err_len, NBODY_E_CUDA, "launch of stage_positions_kernel", e);
     ForceArgs a;
     a.pos = stage; a.partial = partial; a.n_local = (int)n; a.i_slot_begin = 0; a.eps2 = min_r2; a.plan = plan;
+    a.mass_info = nullptr;
     switch (I) {
         case 8: force_fast_kernel<8><<<plan.grid, kThreads, 0, st>>>(a); break;
         case 7: force_fast_kernel<7><<<plan.grid, kThreads, 0, st>>>(a); break;

@@ -291,6 +291,25 @@ def test_full_size_properties(nb, oracle, fast, strict, n):
         assert same_bits(np.ascontiguousarray(s["acceleration"][i:i + 1]), want)
 
 
+def test_uniform_mass_path_agrees_with_general_path(nb, oracle, fast):
+    """Equal masses (every Plummer input) take a shorter inner loop (m_j applied once to the sum);
+    one differing mass switches back to the general loop.  Both must satisfy the fast-mode bar."""
+    p, eps = nb.datasets.plummer_sphere(6000, seed=44)
+    p["mass"] = np.float32(0.75)
+    want = oracle.step_rows(p, 1.5, 0.5, eps, 1)
+    got_u = run_compute_steps(fast, nb, p, 1.5, 0.5, eps, 1)
+    assert rel_err(got_u["acceleration"], want["acceleration"]).max() < 2e-5
+    q = p.copy()
+    q["mass"][4321] = np.float32(0.7500001)
+    want_q = oracle.step_rows(q, 1.5, 0.5, eps, 1)
+    got_g = run_compute_steps(fast, nb, q, 1.5, 0.5, eps, 1)
+    assert rel_err(got_g["acceleration"], want_q["acceleration"]).max() < 2e-5
+    z = p.copy()
+    z["mass"] = 0.0                                   # all-zero masses: uniform, and every force vanishes
+    got_z = run_compute_steps(fast, nb, z, 1.5, 0.5, eps, 1)
+    assert np.all(got_z["acceleration"] == 0)
+
+
 def test_launch_counter_and_timers(nb, fast):
     p, eps = nb.datasets.plummer_sphere(8192, seed=1)
     fast.upload(p)
@@ -300,5 +319,5 @@ def test_launch_counter_and_timers(nb, fast):
     ms, n = fast.force_time()
     fast.profile_force(False)
     assert n == 5 and ms > 0
-    assert fast.launch_count() - before == 10          # force + finish per step
+    assert fast.launch_count() - before == 11          # force + finish per step, + one mass check after the upload
     assert fast.last_step_ms() >= ms * 0.9

@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_force(const float4* __restric
         float4 nxt = make_float4(0,0,0,0);
         if (jt+1<ntiles) nxt = pos[(jt+1)*TJ + tid];
         const float4* A = sA[buf]; const float4* B = sB[buf];
-        if (MODE == 0) {            // packed j-pairs
+        if (MODE == 0 || MODE == 2) {            // packed j-pairs (MODE 2: unit mass)
             #pragma unroll UNROLL
             for (int q=0;q<TJ/2;q++){
                 const float4 a=A[q], b=B[q];
@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_force(const float4* __restric
                     float lo,hi; unpack2(r2,lo,hi);
                     const u64 ri=pack2(rsq(lo),rsq(hi));
                     const u64 ri2=mul2(ri,ri);
-                    const u64 s=mul2(mul2(mj,ri),ri2);
+                    const u64 s = (MODE == 2) ? mul2(ri2, ri) : mul2(mul2(mj,ri),ri2);
                     ax[k]=fma2(dx,s,ax[k]); ay[k]=fma2(dy,s,ay[k]); az[k]=fma2(dz,s,az[k]);
                 }
             }
@@ -109,23 +109,29 @@ int main(int argc, char** argv){
     srand(1); for (auto& p: h){ p.x=rand()/(float)RAND_MAX*100; p.y=rand()/(float)RAND_MAX*100; p.z=rand()/(float)RAND_MAX*100; p.w=1.f; }
     float4 *pos,*out; cudaMalloc(&pos,n*sizeof(float4)); cudaMalloc(&out,n*sizeof(float4));
     cudaMemcpy(pos,h.data(),n*sizeof(float4),cudaMemcpyHostToDevice);
-    run<4,4,256,2,0>("packed", pos,out,n,sm);
-    run<6,2,256,1,0>("packed", pos,out,n,sm);
-    run<6,1,256,1,0>("packed", pos,out,n,sm);
-    run<6,4,256,1,0>("packed", pos,out,n,sm);
+    run<5,1,256,1,0>("packed", pos,out,n,sm);
     run<5,2,256,1,0>("packed", pos,out,n,sm);
-    run<7,2,256,1,0>("packed", pos,out,n,sm);
+    run<5,4,256,1,0>("packed", pos,out,n,sm);
+    run<6,1,256,1,0>("packed", pos,out,n,sm);
+    run<6,2,256,1,0>("packed", pos,out,n,sm);
+    run<6,4,256,1,0>("packed", pos,out,n,sm);
     run<7,1,256,1,0>("packed", pos,out,n,sm);
-    run<6,2,128,1,0>("packed", pos,out,n,sm);
-    run<8,1,128,1,0>("packed", pos,out,n,sm);
-    run<8,2,128,1,0>("packed", pos,out,n,sm);
-    run<10,1,128,1,0>("packed", pos,out,n,sm);
-    run<10,2,128,1,0>("packed", pos,out,n,sm);
-    run<12,1,128,1,0>("packed", pos,out,n,sm);
-    run<12,2,128,1,0>("packed", pos,out,n,sm);
-    run<6,2,128,2,0>("packed", pos,out,n,sm);
-    run<8,1,128,2,0>("packed", pos,out,n,sm);
-    run<6,2,384,1,0>("packed", pos,out,n,sm);
-    run<4,2,384,1,0>("packed", pos,out,n,sm);
+    run<7,2,256,1,0>("packed", pos,out,n,sm);
+    run<7,4,256,1,0>("packed", pos,out,n,sm);
+    run<8,1,256,1,0>("packed", pos,out,n,sm);
+    run<8,2,256,1,0>("packed", pos,out,n,sm);
+    run<8,4,256,1,0>("packed", pos,out,n,sm);
+    run<5,1,256,1,2>("unit", pos,out,n,sm);
+    run<5,2,256,1,2>("unit", pos,out,n,sm);
+    run<5,4,256,1,2>("unit", pos,out,n,sm);
+    run<6,1,256,1,2>("unit", pos,out,n,sm);
+    run<6,2,256,1,2>("unit", pos,out,n,sm);
+    run<6,4,256,1,2>("unit", pos,out,n,sm);
+    run<7,1,256,1,2>("unit", pos,out,n,sm);
+    run<7,2,256,1,2>("unit", pos,out,n,sm);
+    run<7,4,256,1,2>("unit", pos,out,n,sm);
+    run<8,1,256,1,2>("unit", pos,out,n,sm);
+    run<8,2,256,1,2>("unit", pos,out,n,sm);
+    run<8,4,256,1,2>("unit", pos,out,n,sm);
     return 0;
 }
