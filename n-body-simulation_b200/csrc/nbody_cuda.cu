@@ -81,6 +81,13 @@ struct nbody_cuda {
     bool peer_is_ipc[kMaxWorld] = {false};
     int n_attached = 0;
 
+    // CUDA graph of two consecutive steps (single GPU): replayed for long device-resident runs so
+    // that small systems are not bound by launch latency
+    cudaGraphExec_t step_graph = nullptr;
+    float graph_G = 0.f, graph_dt = 0.f, graph_eps2 = 0.f;
+    int graph_parity = 0;
+    bool capturing = false;
+
     // profiling
     bool profile_force = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> force_events;
@@ -114,7 +121,7 @@ int fail(nbody_cuda_t h, int code, const std::string &msg) {
         cudaError_t e__ = cudaGetLastError();                                                    \
         if (e__ != cudaSuccess)                                                                  \
             return fail((h), NBODY_E_CUDA, std::string("launch of ") + name + ": " + cudaGetErrorString(e__)); \
-        (h)->launches++;                                                                         \
+        if (!(h)->capturing) (h)->launches++;                                                    \
     } while (0)
 
 size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -140,8 +147,14 @@ void drop_peers(nbody_cuda_t h) {
     h->n_attached = 0;
 }
 
+void drop_graph(nbody_cuda_t h) {
+    if (h->step_graph) cudaGraphExecDestroy(h->step_graph);
+    h->step_graph = nullptr;
+}
+
 void free_buffers(nbody_cuda_t h) {
     drop_peers(h);
+    drop_graph(h);
     if (h->block) cudaFree(h->block);
     if (h->vel) cudaFree(h->vel);
     if (h->acc) cudaFree(h->acc);
@@ -420,6 +433,7 @@ int nbody_cuda_configure(nbody_cuda_t h, size_t n_total, int rank, int world) {
 
     CU_TRY(h, cudaStreamSynchronize(h->stream));
     drop_peers(h);          // tokens describe the old block
+    drop_graph(h);          // so does a captured step
     size_t begin, count;
     slice_of(n_total, world, rank, &begin, &count);
     size_t max_count = n_total / world + (n_total % world ? 1 : 0);
@@ -521,8 +535,38 @@ int nbody_cuda_step(nbody_cuda_t h, float G, float dt, float min_r2, int n_steps
     if (h->world > 1 && !all_peers_attached(h))
         return fail(h, NBODY_E_STATE, "nbody_cuda_step: world > 1 needs every peer attached (or use nbody_cuda_step_local + an all-gather)");
     CU_TRY(h, cudaSetDevice(h->device));
+    int done = 0;
+    const bool use_graph = h->world == 1 && !h->profile_force && n_steps >= 4 && h->n_local > 0;
+    if (use_graph) {
+        int rc = ensure_mass_info(h);           // outside the capture: it runs once per upload
+        if (rc != NBODY_OK) return rc;
+        if (h->step_graph && (h->graph_G != G || h->graph_dt != dt || h->graph_eps2 != min_r2 || h->graph_parity != h->cur))
+            drop_graph(h);
+        if (!h->step_graph) {
+            // two steps = one full turn of the double-buffered positions, so the graph can be replayed
+            cudaGraph_t g = nullptr;
+            CU_TRY(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+            h->capturing = true;
+            rc = one_step(h, G, dt, min_r2, true);
+            if (rc == NBODY_OK) rc = one_step(h, G, dt, min_r2, true);
+            h->capturing = false;
+            cudaError_t e = cudaStreamEndCapture(h->stream, &g);
+            if (rc != NBODY_OK) { if (g) cudaGraphDestroy(g); return rc; }
+            CU_TRY(h, e);
+            e = cudaGraphInstantiate(&h->step_graph, g, 0);
+            cudaGraphDestroy(g);
+            CU_TRY(h, e);
+            h->graph_G = G; h->graph_dt = dt; h->graph_eps2 = min_r2; h->graph_parity = h->cur;
+        }
+    }
     CU_TRY(h, cudaEventRecord(h->ev_begin, h->stream));
-    for (int s = 0; s < n_steps; ++s) {
+    if (use_graph) {
+        for (; done + 2 <= n_steps; done += 2) {
+            CU_TRY(h, cudaGraphLaunch(h->step_graph, h->stream));
+            h->launches += 4;                   // force + finish, twice
+        }
+    }
+    for (; done < n_steps; ++done) {
         int rc = one_step(h, G, dt, min_r2, true);
         if (rc != NBODY_OK) return rc;
     }
