@@ -79,6 +79,11 @@ int nbody_cuda_upload_aos(nbody_cuda_t h, const void *particles, size_t count);
  * Replaces the per-step MPI_Gatherv of src/apps/headless_main.cpp:368-373. */
 int nbody_cuda_download_aos(nbody_cuda_t h, void *particles, size_t count);
 
+/* Positions only, as packed float[count][3]: exactly one record of the reference's trajectory file
+ * (src/CheckpointManager.cpp:86-99 builds the same array from the AoS vector), 12 instead of 40
+ * bytes per particle over PCIe. */
+int nbody_cuda_download_positions(nbody_cuda_t h, float *xyz, size_t count);
+
 /* n_steps x { force accumulation over all n_total sources for the local targets;
  * v += a*dt; x += v*dt }  -- src/NaiveSimulation.cpp:7-51 / src/MpiNaiveSimulation.cpp:10-141.
  * Device-resident: no host traffic.  With world > 1 this requires attached peers

@@ -51,6 +51,7 @@ SIGNATURES = {
     "nbody_cuda_slice": (_i, [_vp, C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz)]),
     "nbody_cuda_upload_aos": (_i, [_vp, _vp, _sz]),
     "nbody_cuda_download_aos": (_i, [_vp, _vp, _sz]),
+    "nbody_cuda_download_positions": (_i, [_vp, _vp, _sz]),
     "nbody_cuda_step": (_i, [_vp, _f, _f, _f, _i]),
     "nbody_cuda_step_local": (_i, [_vp, _f, _f, _f]),
     "nbody_cuda_compute_step_aos": (_i, [_vp, _vp, _sz, _f, _f, _f]),

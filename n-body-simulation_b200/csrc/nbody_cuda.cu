@@ -528,6 +528,24 @@ int nbody_cuda_download_aos(nbody_cuda_t h, void *particles, size_t count) {
     return check_fault(h);
 }
 
+int nbody_cuda_download_positions(nbody_cuda_t h, float *xyz, size_t count) {
+    if (!h) return NBODY_E_INVALID;
+    if (!h->configured) return fail(h, NBODY_E_STATE, "nbody_cuda_download_positions: not configured");
+    if (count != h->n_local) return fail(h, NBODY_E_INVALID, "nbody_cuda_download_positions: count differs from the configured slice");
+    if (count && !xyz) return fail(h, NBODY_E_INVALID, "nbody_cuda_download_positions: xyz is NULL");
+    CU_TRY(h, cudaSetDevice(h->device));
+    if (count == 0) return NBODY_OK;
+    const size_t bytes = count * 3 * sizeof(float);
+    int rc = ensure_aos(h, bytes);
+    if (rc != NBODY_OK) return rc;
+    pack_positions_kernel<<<(int)((count + kThreads - 1) / kThreads), kThreads, 0, h->stream>>>(
+        reinterpret_cast<float *>(h->d_aos), (int)count, (int)(h->rank * h->slot_stride), h->pos[h->cur]);
+    CHECK_LAUNCH(h, "pack_positions_kernel");
+    CU_TRY(h, cudaMemcpyAsync(xyz, h->d_aos, bytes, cudaMemcpyDeviceToHost, h->stream));
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_fault(h);
+}
+
 int nbody_cuda_step(nbody_cuda_t h, float G, float dt, float min_r2, int n_steps) {
     if (!h) return NBODY_E_INVALID;
     if (!h->configured) return fail(h, NBODY_E_STATE, "nbody_cuda_step: not configured");

@@ -83,6 +83,10 @@ __host__ __device__ __forceinline__ int plan_owner(const ForcePlan &p, long long
     return (int)(((u + 1) * p.grid + p.units - 1) / p.units) - 1;
 }
 
+#ifdef NBODY_TILE_INTERACT_OVERRIDE
+// tuning hook (tools/exp/tune_fast.cu): an experiment supplies its own tile_interact
+#include NBODY_TILE_INTERACT_OVERRIDE
+#else
 // One source tile against the I targets of this thread, packed two sources per instruction.
 // smem tile layout: A[q] = {x[2q], x[2q+1], y[2q], y[2q+1]},  B[q] = {z[2q], z[2q+1], m[2q], m[2q+1]}.
 // Per source pair and target: 3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 3 FMUL2 + 3 FFMA2.
@@ -124,6 +128,8 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
         }
     }
 }
+
+#endif  // NBODY_TILE_INTERACT_OVERRIDE
 
 struct ForceArgs {
     const float4 *pos;     // current global positions, n_slots
@@ -460,6 +466,23 @@ __global__ void __launch_bounds__(kThreads) soa_to_aos_kernel(float *__restrict_
     __syncthreads();
     float *dst = aos + (size_t)first * kRecFloats;
     for (int k = threadIdx.x; k < cnt * kRecFloats; k += kThreads) dst[k] = s[k];
+}
+
+// Positions of the local slice as packed float[n][3] -- the record layout of the reference's
+// trajectory file (src/CheckpointManager.cpp:86-99) -- staged through shared memory so the
+// 12-byte side is written coalesced.
+__global__ void __launch_bounds__(kThreads) pack_positions_kernel(float *__restrict__ xyz, int n, int slot_begin,
+                                                                  const float4 *__restrict__ pos) {
+    __shared__ float s[kThreads * 3];
+    const int first = blockIdx.x * kThreads;
+    const int cnt = min(kThreads, n - first);
+    if (threadIdx.x < cnt) {
+        const float4 p = pos[slot_begin + first + threadIdx.x];
+        s[3 * threadIdx.x + 0] = p.x; s[3 * threadIdx.x + 1] = p.y; s[3 * threadIdx.x + 2] = p.z;
+    }
+    __syncthreads();
+    float *dst = xyz + (size_t)first * 3;
+    for (int k = threadIdx.x; k < cnt * 3; k += kThreads) dst[k] = s[k];
 }
 
 // Fills position slots [begin, end) with zero-mass padding.

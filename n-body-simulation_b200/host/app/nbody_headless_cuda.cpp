@@ -11,7 +11,8 @@
 //   --plummer N          Plummer sphere input (the reference's MPI build uses it for --random, :191-195)
 //   --seed S             seed the reference's generator engine (Random.hpp:7) for reproducible inputs
 //   --mode fast|strict   arithmetic mode of the CUDA kernels (default fast)
-//   --device D           CUDA ordinal
+//   --device D           CUDA ordinal of the first GPU
+//   --gpus P             spread the particles over GPUs D .. D+P-1 (slices as headless_main.cpp:249-259)
 //   --resident           keep the state on the GPU between steps (no per-step host round trip);
 //                        positions come back only when a trajectory record is due
 //   --checkpoint-every K write a trajectory record every K-th step only (default 1, as the reference)
@@ -23,6 +24,8 @@
 #include <iostream>
 #include <memory>
 #include <string>
+#include <vector>
+#include <algorithm>
 
 #include "CheckpointManager.h"
 #include "CudaNaiveSimulation.h"
@@ -41,7 +44,7 @@ struct Options {
     std::size_t disk_n = 0, plummer_n = 0;
     bool solar = false, write_output = true, resident = false, seeded = false;
     unsigned seed = 0;
-    int device = 0;
+    int device = 0, gpus = 1;
     std::size_t checkpoint_every = 1, energy_every = 0;
     CudaNaiveSimulation::Mode mode = CudaNaiveSimulation::Mode::Fast;
     SimParams params;
@@ -65,6 +68,7 @@ Options parse(int argc, char **argv) {
         else if (a == "--seed") { o.seed = (unsigned)std::stoul(next(i)); o.seeded = true; }
         else if (a == "--mode") o.mode = (next(i) == "strict") ? CudaNaiveSimulation::Mode::Strict : CudaNaiveSimulation::Mode::Fast;
         else if (a == "--device") o.device = std::stoi(next(i));
+        else if (a == "--gpus") o.gpus = std::max(1, std::stoi(next(i)));
         else if (a == "--resident") o.resident = true;
         else if (a == "--checkpoint-every") o.checkpoint_every = std::max<std::size_t>(1, std::stoul(next(i)));
         else if (a == "--energy-every") o.energy_every = std::stoul(next(i));
@@ -81,7 +85,9 @@ int main(int argc, char **argv) {
     if (opt.seeded) getRandomEngine().seed(opt.seed);
 
     std::cout << "CudaNaiveSimulation (" << (opt.mode == CudaNaiveSimulation::Mode::Strict ? "strict" : "fast") << ")\n";
-    auto algo_owner = std::make_unique<CudaNaiveSimulation>(opt.device, opt.mode);
+    std::vector<int> devices;
+    for (int d = 0; d < opt.gpus; ++d) devices.push_back(opt.device + d);
+    auto algo_owner = std::make_unique<CudaNaiveSimulation>(devices, opt.mode);
     CudaNaiveSimulation *algo = algo_owner.get();            // kept for the device-resident extension
     NBodySimulation sim(std::move(algo_owner), opt.params);  // the reference facade, unchanged
     sim.setDt(opt.params.dt);
@@ -135,7 +141,7 @@ int main(int argc, char **argv) {
     const auto t1 = std::chrono::high_resolution_clock::now();
     const double seconds = std::chrono::duration<double>(t1 - t0).count();
 
-    logger.log(n, opt.steps, seconds);
+    logger.log(n, opt.steps, seconds, (std::size_t)opt.gpus);   // workers column, as the MPI build logs its rank count
     std::cout << "Simulation completed in " << seconds << " seconds\n";
     std::printf("%.4e pairwise interactions/s (N^2 * steps / seconds), %lld kernel launches\n",
                 (double)n * (double)n * (double)opt.steps / seconds, algo->kernelLaunches());

@@ -198,6 +198,14 @@ class CudaNaiveSimulation:
         p = _as_particles(particles)
         self._ck(self._lib.nbody_cuda_download_aos(self._h, p.ctypes.data_as(C.c_void_p), p.shape[0]))
 
+    def download_positions(self) -> np.ndarray:
+        """(count, 3) float32 positions of the local slice: one record of the reference's trajectory
+        file (src/CheckpointManager.cpp:86-99) without the 40-byte AoS detour."""
+        n = self.slice()["count"]
+        out = np.empty((n, 3), np.float32)
+        self._ck(self._lib.nbody_cuda_download_positions(self._h, out.ctypes.data_as(C.c_void_p), n))
+        return out
+
     def synchronize(self) -> None:
         self._ck(self._lib.nbody_cuda_synchronize(self._h))
 

@@ -12,6 +12,7 @@
 #include "CudaNaiveSimulation.h"
 
 extern "C" void oracle_naive_step_rows_f32(void *p, size_t n, float G, float dt, float eps2, int steps);
+extern "C" int nbody_cuda_device_count(void);
 
 static std::vector<particle_t> make(size_t n, unsigned seed) {
     std::mt19937 rng(seed);
@@ -70,6 +71,45 @@ int main() {
         fast.energy(params, k, u);
         EXPECT(k > 0 && u < 0, "energy signs");
         EXPECT(fast.lastStepMilliseconds() > 0 && fast.kernelLaunches() > 0, "timers");
+    }
+    // several GPUs driven from this one thread: strict mode gives the same bits as one GPU
+    {
+        const int ndev = nbody_cuda_device_count();
+        for (int world : {2, 4, 8}) {
+            if (ndev < world) { std::printf("skip %d-GPU check (%d visible)\n", world, ndev); continue; }
+            std::vector<int> devs;
+            for (int d = 0; d < world; ++d) devs.push_back(d);
+            for (auto mode : {CudaNaiveSimulation::Mode::Strict, CudaNaiveSimulation::Mode::Fast}) {
+                std::unique_ptr<SimulationAlgorithm> algo = std::make_unique<CudaNaiveSimulation>(devs, mode);
+                for (size_t n : {size_t(10007), size_t(3), size_t(65536)}) {
+                    auto p = make(n, 777 + (unsigned)n), want = p;
+                    for (int s = 0; s < 3; ++s) algo->computeStep(p, params);
+                    oracle_naive_step_rows_f32(want.data(), n, params.G, params.dt, params.min_r2, 3);
+                    if (mode == CudaNaiveSimulation::Mode::Strict) {
+                        EXPECT(std::memcmp(p.data(), want.data(), n * sizeof(particle_t)) == 0, "%d-GPU strict differs at n=%zu", world, n);
+                    } else {
+                        double worst = 0;
+                        for (size_t i = 0; i < n; ++i) {
+                            const float *a = &p[i].position.x, *b = &want[i].position.x;
+                            double num = 0, den = 0;
+                            for (int c = 0; c < 3; ++c) { num += double(a[c] - b[c]) * (a[c] - b[c]); den += double(b[c]) * b[c]; }
+                            worst = std::fmax(worst, std::sqrt(num / den));
+                        }
+                        EXPECT(worst < 1e-5, "%d-GPU fast position error %.3g at n=%zu", world, worst, n);
+                    }
+                }
+                auto *cuda = static_cast<CudaNaiveSimulation *>(algo.get());
+                auto p = make(40000, 5), q = p;
+                cuda->upload(p);
+                cuda->steps(params, 5);
+                cuda->download(p);
+                CudaNaiveSimulation one(0, mode);
+                one.upload(q); one.steps(params, 5); one.download(q);
+                if (mode == CudaNaiveSimulation::Mode::Strict)
+                    EXPECT(std::memcmp(p.data(), q.data(), p.size() * sizeof(particle_t)) == 0, "%d-GPU resident run differs from 1 GPU", world);
+                std::printf("%d GPUs %s: ok so far (%d failures)\n", world, mode == CudaNaiveSimulation::Mode::Strict ? "strict" : "fast", fails);
+            }
+        }
     }
     // errors are exceptions, not exits
     try {

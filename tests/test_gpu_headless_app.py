@@ -67,3 +67,13 @@ def test_fast_mode_run_reports_energy_and_rate(app, tmp_path):
     e = [float(x) for x in re.findall(r"E = ([-+0-9.e]+)", out)]
     assert len(e) == 3 and abs(e[2] - e[0]) / abs(e[0]) < 1e-2
     assert re.search(r"pairwise interactions/s", out) and not os.path.exists(tmp_path / "simulation_output.bin")
+
+
+def test_two_gpus_same_trajectory_as_one(app, nb, tmp_path):
+    if nb.load_library().nbody_cuda_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    common = ["--plummer", "20000", "--steps", "8", "--seed", "3", "--mode", "strict", "--resident", "--checkpoint-every", "4"]
+    run_app(tmp_path, *common, "--checkpoint", "one.bin", "--out", "one.csv")
+    run_app(tmp_path, *common, "--gpus", "2", "--checkpoint", "two.bin", "--out", "two.csv")
+    assert open(tmp_path / "one.bin", "rb").read() == open(tmp_path / "two.bin", "rb").read()
+    assert open(tmp_path / "two.csv").read().strip().endswith(",2")

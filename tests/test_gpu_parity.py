@@ -321,3 +321,39 @@ def test_launch_counter_and_timers(nb, fast):
     assert n == 5 and ms > 0
     assert fast.launch_count() - before == 11          # force + finish per step, + one mass check after the upload
     assert fast.last_step_ms() >= ms * 0.9
+
+
+# ------------------------------------------------------------------------------------------------
+# data formats around the path: trajectory records straight from the device, exact restart
+# ------------------------------------------------------------------------------------------------
+def test_trajectory_from_device_positions_matches_reference_writer(nb, reference, strict, tmp_path):
+    n, steps = 2500, 6
+    p, eps = reference.disk(n, 77)
+    params = nb.SimParams(1.0, 0.5, eps)
+    ours, theirs = str(tmp_path / "ours.bin"), str(tmp_path / "ref.bin")
+    w = nb.TrajectoryWriter(ours, p["mass"], steps)
+    reference.checkpoint_begin(theirs, p, steps)
+    strict.upload(p.copy())
+    q = p
+    for _ in range(steps):
+        strict.step(params, 1)
+        w.write_step(strict.download_positions())          # 12 B/particle, no AoS
+        q = reference.naive_steps(q, 1.0, 0.5, eps, 1)
+        reference.checkpoint_write_step(theirs, q)
+    assert open(ours, "rb").read() == open(theirs, "rb").read()
+
+
+@pytest.mark.parametrize("mode", ["strict", "fast"])
+def test_restart_record_resumes_bit_exactly(nb, strict, fast, mode, tmp_path):
+    sim = strict if mode == "strict" else fast
+    p, eps = nb.datasets.plummer_sphere(9000, seed=12)
+    params = nb.SimParams(1.0, 0.5, eps)
+    whole = p.copy()
+    sim.upload(whole); sim.step(params, 12); sim.download(whole)
+    half = p.copy()
+    sim.upload(half); sim.step(params, 5); sim.download(half)
+    path = str(tmp_path / "run.restart")
+    nb.write_restart(path, half, params, 5)
+    again, params2, step = nb.read_restart(path)
+    sim.upload(again); sim.step(params2, 12 - step); sim.download(again)
+    assert again.tobytes() == whole.tobytes()
