@@ -47,7 +47,7 @@ def parse():
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=0, help="override the particle count of the workload")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"])
-    ap.add_argument("--mode", default="fast", choices=["fast", "strict"])
+    ap.add_argument("--mode", default="fast", choices=["fast", "strict", "fp64"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--ref-n", type=int, default=0, help="sample size of the reference arm (default: chosen to bound its run time)")
@@ -300,7 +300,8 @@ def run_ours(args):
         pass
     props = torch.cuda.get_device_properties(local_rank)
     sm_max_mhz = float(peaks.get("sm_max_mhz") or clocks.get("sm_max_mhz") or 1965.0)
-    nominal_peak = props.multi_processor_count * SM_LANES * 2 * sm_max_mhz * 1e6 / 1e12
+    lanes = 64 if args.mode == "fp64" else SM_LANES          # B200: 64 FP64 lanes per SM
+    nominal_peak = props.multi_processor_count * lanes * 2 * sm_max_mhz * 1e6 / 1e12
     measured_fma = sim.measure_fma_peak(True) / 1e12
     flop_per_launch = FLOP_PER_INTERACTION * float(cnt) * float(n)
     achieved = flop_per_launch / (force_ms / max(force_launches, 1) * 1e-3) / 1e12 if force_launches else None
@@ -312,9 +313,9 @@ def run_ours(args):
         except Exception:
             traffic = None
     roofline = {
-        "bound": "fp32_fma", "kernel": f"force_{args.mode}_kernel", "achieved": achieved, "peak": nominal_peak,
+        "bound": "fp64_fma" if args.mode == "fp64" else "fp32_fma", "kernel": f"force_{args.mode}_kernel", "achieved": achieved, "peak": nominal_peak,
         "unit": "TFLOP/s", "frac": (achieved / nominal_peak) if achieved else None, "traffic": traffic,
-        "peak_source": f"{props.multi_processor_count} SMs x 128 FP32 lanes x 2 flop x {sm_max_mhz:.0f} MHz "
+        "peak_source": f"{props.multi_processor_count} SMs x {lanes} {'FP64' if args.mode == 'fp64' else 'FP32'} lanes x 2 flop x {sm_max_mhz:.0f} MHz "
                        "(sm_max_mhz of MEASURED_PEAKS.json, which holds no FP32 figure); tensor cores unused by design",
         "measured_ffma2_chain_tflops": measured_fma,
         "frac_of_measured_ffma2_chain": (achieved / measured_fma) if achieved else None,
@@ -338,7 +339,7 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
+            "dtype": "f64" if args.mode == "fp64" else "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {mirrors}", "n": n, "generator": gen, "G": 1.0, "dt": 0.5,
                        "min_r2": eps, "mode": args.mode, "exchange": args.exchange if world > 1 else "none",
                        "parallelism": f"i-slice x{world}", "l2": "flushed between steps (160 MiB memset, inside the timed region)",

@@ -39,6 +39,7 @@ typedef struct nbody_cuda *nbody_cuda_t;
 /* arithmetic modes */
 #define NBODY_MODE_FAST 0   /* FP32, packed FFMA2 + MUFU.RSQ, blocked summation (the product)            */
 #define NBODY_MODE_STRICT 1 /* FP32, the reference's exact operation order and rounding: bit-identical */
+#define NBODY_MODE_FP64 2   /* forces summed in FP64 from the FP32 state, rounded to FP32 once; optional, no counterpart */
 
 /* Size of the record this library reads and writes; equals sizeof(particle_t) = 40
  * (include/Particle.hpp:53-59). */

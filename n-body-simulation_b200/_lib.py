@@ -17,6 +17,7 @@ HEADER = os.path.join(os.path.dirname(HERE), "include", "nbody_cuda.h")
 NBODY_OK = 0
 MODE_FAST = 0
 MODE_STRICT = 1
+MODE_FP64 = 2
 PEER_HANDLE_BYTES = 128
 
 

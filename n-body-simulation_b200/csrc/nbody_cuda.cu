@@ -254,16 +254,22 @@ int launch_force(nbody_cuda_t h, float G, float min_r2) {
         h->force_events_used++;
         CU_TRY(h, cudaEventRecord(e0, h->stream));
     }
-    if (h->mode == NBODY_MODE_STRICT) {
+    if (h->mode == NBODY_MODE_STRICT || h->mode == NBODY_MODE_FP64) {
         StrictArgs a;
         a.pos = h->pos[h->cur]; a.acc = h->acc;
         a.n_local = (int)h->n_local; a.i_slot_begin = (int)(h->rank * h->slot_stride);
         a.world = h->world; a.slot_stride = (int)h->slot_stride;
         for (int r = 0; r < kMaxWorld; ++r) a.counts[r] = h->counts[r];
         a.G = G; a.eps2 = min_r2;
-        const int grid = (int)((h->n_local + kThreads - 1) / kThreads);
-        force_strict_kernel<<<grid, kThreads, 0, h->stream>>>(a);
-        CHECK_LAUNCH(h, "force_strict_kernel");
+        if (h->mode == NBODY_MODE_FP64) {
+            const int grid = (int)((h->n_local + 2 * kThreads - 1) / (2 * kThreads));
+            force_fp64_kernel<<<grid, kThreads, 0, h->stream>>>(a);
+            CHECK_LAUNCH(h, "force_fp64_kernel");
+        } else {
+            const int grid = (int)((h->n_local + kThreads - 1) / kThreads);
+            force_strict_kernel<<<grid, kThreads, 0, h->stream>>>(a);
+            CHECK_LAUNCH(h, "force_strict_kernel");
+        }
     } else {
         ForceArgs a;
         a.pos = h->pos[h->cur]; a.partial = h->partial;
@@ -339,7 +345,7 @@ int launch_finish(nbody_cuda_t h, float G, float dt, bool publish) {
     a.mass_info = h->flags + kMassInfoWord;
     if (publish) fill_peer_ptrs(h, h->cur ^ 1, a.peer_next, &a.n_peers);
     const int grid = (int)((h->n_local + kThreads - 1) / kThreads);
-    if (h->mode == NBODY_MODE_STRICT) finish_kernel<false><<<grid, kThreads, 0, h->stream>>>(a);
+    if (h->mode != NBODY_MODE_FAST) finish_kernel<false><<<grid, kThreads, 0, h->stream>>>(a);
     else finish_kernel<true><<<grid, kThreads, 0, h->stream>>>(a);
     CHECK_LAUNCH(h, "finish_kernel");
     return NBODY_OK;
@@ -380,7 +386,7 @@ int nbody_cuda_device_count(void) {
 int nbody_cuda_create(nbody_cuda_t *out, int device, int mode) {
     if (!out) return fail(nullptr, NBODY_E_INVALID, "nbody_cuda_create: out is NULL");
     *out = nullptr;
-    if (mode != NBODY_MODE_FAST && mode != NBODY_MODE_STRICT)
+    if (mode != NBODY_MODE_FAST && mode != NBODY_MODE_STRICT && mode != NBODY_MODE_FP64)
         return fail(nullptr, NBODY_E_INVALID, "nbody_cuda_create: unknown mode");
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);

@@ -294,6 +294,57 @@ __global__ void __launch_bounds__(kThreads) force_strict_kernel(const StrictArgs
 }
 
 // ---------------------------------------------------------------------------------------------
+// FP64 force kernel (optional variant, reported separately: the reference has no double).
+// Same formula evaluated in double from the FP32 positions and masses, sources in ascending slot
+// order, self skipped by index; the sum is rounded to FP32 once, at the end, because the state the
+// reference keeps (include/Particle.hpp:53-59) is FP32.  Two targets per thread; source tiles are
+// converted to double once per CTA on their way into shared memory.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) force_fp64_kernel(const StrictArgs a) {
+    __shared__ double4 tile[kTileJ];
+    const int tid = threadIdx.x;
+    const int l0 = blockIdx.x * (2 * kThreads) + tid, l1 = l0 + kThreads;
+    const bool live0 = l0 < a.n_local, live1 = l1 < a.n_local;
+    const int slot0 = a.i_slot_begin + (live0 ? l0 : 0), slot1 = a.i_slot_begin + (live1 ? l1 : 0);
+    const float4 p0 = a.pos[slot0], p1 = a.pos[slot1];
+    const double x0 = p0.x, y0 = p0.y, z0 = p0.z, x1 = p1.x, y1 = p1.y, z1 = p1.z;
+    const double eps2 = (double)a.eps2;
+    double ax0 = 0, ay0 = 0, az0 = 0, ax1 = 0, ay1 = 0, az1 = 0;
+    const int n_slots = a.world * a.slot_stride;
+    for (int j0 = 0; j0 < n_slots; j0 += kTileJ) {
+        __syncthreads();
+        {
+            const float4 q = a.pos[j0 + tid];       // padding has mass 0: contributes exactly 0
+            tile[tid] = make_double4((double)q.x, (double)q.y, (double)q.z, (double)q.w);
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int jj = 0; jj < kTileJ; ++jj) {
+            const double4 q = tile[jj];
+            {
+                const double dx = q.x - x0, dy = q.y - y0, dz = q.z - z0;
+                const double r2 = fma(dx, dx, fma(dy, dy, fma(dz, dz, eps2)));
+                const double ri = rsqrt(r2);
+                double s = q.w * ri * ri * ri;
+                s = (j0 + jj == slot0) ? 0.0 : s;
+                ax0 = fma(dx, s, ax0); ay0 = fma(dy, s, ay0); az0 = fma(dz, s, az0);
+            }
+            {
+                const double dx = q.x - x1, dy = q.y - y1, dz = q.z - z1;
+                const double r2 = fma(dx, dx, fma(dy, dy, fma(dz, dz, eps2)));
+                const double ri = rsqrt(r2);
+                double s = q.w * ri * ri * ri;
+                s = (j0 + jj == slot1) ? 0.0 : s;
+                ax1 = fma(dx, s, ax1); ay1 = fma(dy, s, ay1); az1 = fma(dz, s, az1);
+            }
+        }
+    }
+    const double G = (double)a.G;
+    if (live0) a.acc[l0] = make_float4((float)(G * ax0), (float)(G * ay0), (float)(G * az0), 0.0f);
+    if (live1) a.acc[l1] = make_float4((float)(G * ax1), (float)(G * ay1), (float)(G * az1), 0.0f);
+}
+
+// ---------------------------------------------------------------------------------------------
 // Finishing kernel: (fast mode) add the segment partials of each target in ascending segment
 // order and scale by G; then the reference's semi-implicit Euler step, each product and sum
 // rounded separately (src/NaiveSimulation.cpp:47-50); then publish the new {x,y,z,m} to the

@@ -66,16 +66,16 @@ class _DeviceFloats:
 class CudaNaiveSimulation:
     """Drop-in for ``NaiveSimulation`` / ``MpiNaiveSimulation`` on one B200 per process.
 
-    mode      "fast" (packed-FP32 kernel, the product) or "strict" (the reference's exact
-              operation order: bit-identical results).
+    mode      "fast" (packed-FP32 kernel, the product), "strict" (the reference's exact operation
+              order: bit-identical results) or "fp64" (forces summed in double; optional variant).
     group     a ``torch.distributed`` process group, or None for a single GPU.
     exchange  "p2p" | "nccl" (only with a group).
     """
 
     def __init__(self, device: int | None = None, mode: str = "fast", group=None, exchange: str = "p2p"):
         self._lib = _lib.load_library()
-        if mode not in ("fast", "strict"):
-            raise ValueError("mode must be 'fast' or 'strict'")
+        if mode not in ("fast", "strict", "fp64"):
+            raise ValueError("mode must be 'fast', 'strict' or 'fp64'")
         if exchange not in ("p2p", "nccl"):
             raise ValueError("exchange must be 'p2p' or 'nccl'")
         self.mode = mode
@@ -97,7 +97,7 @@ class CudaNaiveSimulation:
                 device = int(os.environ.get("LOCAL_RANK", self.rank))
         self.device = device
         h = C.c_void_p()
-        code = self._lib.nbody_cuda_create(C.byref(h), device, _lib.MODE_STRICT if mode == "strict" else _lib.MODE_FAST)
+        code = self._lib.nbody_cuda_create(C.byref(h), device, {"fast": _lib.MODE_FAST, "strict": _lib.MODE_STRICT, "fp64": _lib.MODE_FP64}[mode])
         _lib.check(self._lib, None, code)
         self._h = h
         self.n_total = None

@@ -357,3 +357,35 @@ def test_restart_record_resumes_bit_exactly(nb, strict, fast, mode, tmp_path):
     again, params2, step = nb.read_restart(path)
     sim.upload(again); sim.step(params2, 12 - step); sim.download(again)
     assert again.tobytes() == whole.tobytes()
+
+
+# ------------------------------------------------------------------------------------------------
+# optional FP64 variant: forces summed in double, state stays FP32 (reported separately in bench.py)
+# ------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def fp64(nb):
+    s = nb.CudaNaiveSimulation(mode="fp64")
+    yield s
+    s.close()
+
+
+@pytest.mark.parametrize("kind,n", [("plummer", 5000), ("disk", 4096)])
+def test_fp64_mode_matches_fp64_truth_to_one_float_rounding(nb, oracle, fp64, kind, n):
+    p, eps = (nb.datasets.plummer_sphere if kind == "plummer" else nb.datasets.galaxy_disk)(n, seed=3)
+    truth = oracle.accel_f64(p, 1.0, eps)
+    got = run_compute_steps(fp64, nb, p, 1.0, 0.5, eps, 1)
+    e = rel_err(got["acceleration"], truth)
+    assert e.max() < 1.2e-7            # the only error left is the final rounding to binary32 (2^-24 per component)
+
+
+def test_fast_mode_against_gpu_fp64_at_config3_size(nb, fast, fp64):
+    """Accuracy of the fast kernel at N=262144 (BASELINE configs[2]), where the CPU truth is too slow:
+    the FP64 GPU variant (itself pinned on the CPU FP64 oracle above) is the yardstick."""
+    n = 262144
+    p, eps = nb.datasets.plummer_sphere(n, seed=12345)
+    params = nb.SimParams(1.0, 0.5, eps)
+    a = run_compute_steps(fast, nb, p, 1.0, 0.5, eps, 1)["acceleration"]
+    b = run_compute_steps(fp64, nb, p, 1.0, 0.5, eps, 1)["acceleration"]
+    e = rel_err(a, b)
+    print("fast vs fp64 at N=262144: max %.3g median %.3g" % (e.max(), np.median(e)))
+    assert np.median(e) < 2e-6 and e.max() < 5e-5
