@@ -45,7 +45,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
-    ap.add_argument("--n", type=int, default=0, help="override the particle count of the workload")
+    ap.add_argument("--particles", type=int, default=0,
+                    help="override the particle count of the workload (not --n: torchrun would read that as one of its own options)")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"])
     ap.add_argument("--mode", default="fast", choices=["fast", "strict", "fp64"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -56,8 +57,8 @@ def parse():
 
 def workload_config(args):
     n, gen, mirrors = WORKLOADS[args.workload]
-    if args.n:
-        n = args.n
+    if args.particles:
+        n = args.particles
     return n, gen, mirrors
 
 
