@@ -1,0 +1,107 @@
+"""Turns the ncu artefacts brought back in gpurun_out/ into the tracked summaries under profiles/.
+
+    python tools/summarize_profiles.py <tag> <launches.csv> <full.ncu-rep> "<command that was profiled>"
+
+Writes profiles/<tag>_launches.csv (copy), profiles/<tag>_launches_summary.md,
+profiles/<tag>_force_fast_ncu.md and updates profiles/force_kernel_traffic.json (read by bench.py
+for roofline.traffic).
+"""
+import collections
+import csv
+import io
+import json
+import os
+import shutil
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PROF = os.path.join(ROOT, "profiles")
+
+WANT = [
+    "gpu__time_duration.sum", "sm__cycles_elapsed.avg.per_second", "dram__bytes_read.sum", "dram__bytes_write.sum",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_sector_hit_rate.pct",
+    "launch__grid_size", "launch__block_size", "launch__registers_per_thread", "launch__occupancy_limit_registers",
+    "sm__warps_active.avg.per_cycle_active", "smsp__warps_active.avg.per_cycle_active", "smsp__inst_executed.sum",
+    "smsp__cycles_active.avg", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+    "smsp__average_warp_latency_per_inst_issued.ratio",
+    "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+]
+UNIT = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+
+def launches(tag, path, command):
+    txt = open(path).read()
+    txt = txt[txt.index('"ID"'):]
+    rows = list(csv.DictReader(io.StringIO(txt)))
+    agg = collections.OrderedDict()
+    for r in rows:
+        k = r["Kernel Name"].split("(")[0].replace("void ", "")
+        a = agg.setdefault(k, [0, 0.0, r["Grid Size"], r["Block Size"]])
+        a[0] += 1
+        a[1] += float(r["Metric Value"])
+    tot = sum(a[1] for a in agg.values())
+    fk = [k for k in agg if "force_" in k][0]
+    out = [f"# {tag} — ncu launch list of `{command}`", "",
+           "`ncu --metrics gpu__time_duration.sum --clock-control none -c 400` (per-launch times are cold-cache and "
+           "serialised: compare SHARES, not absolutes).", f"Raw list: `profiles/{tag}_launches.csv`.", "",
+           "| kernel | launches | total ms | share | grid | block |", "|---|---|---|---|---|---|"]
+    for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        out.append(f"| `{k}` | {a[0]} | {a[1] / 1e6:.3f} | {100 * a[1] / tot:.3f} % | {a[2]} | {a[3]} |")
+    out += ["", f"Total device time in the listed launches: {tot / 1e6:.1f} ms; the force kernel is "
+                f"{100 * agg[fk][1] / tot:.2f} % of it ({agg[fk][1] / agg[fk][0] / 1e6:.2f} ms per launch).",
+            "`fma_peak_kernel` is bench.py's FFMA2 micro-benchmark (outside the timed region); "
+            "`at::vectorized_elementwise_kernel<FillFunctor>` is the L2 flush bench.py issues between timed steps (torch, not ours)."]
+    shutil.copy(path, os.path.join(PROF, f"{tag}_launches.csv"))
+    open(os.path.join(PROF, f"{tag}_launches_summary.md"), "w").write("\n".join(out) + "\n")
+    return agg[fk][1] / tot
+
+
+def full(tag, rep, command, key):
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    name = data[0][hdr.index("Kernel Name")] if "Kernel Name" in hdr else "force kernel"
+    vals = {h: (data[0][i], units[i]) for i, h in enumerate(hdr)}
+    out = [f"# {tag} — `ncu --set full` of `{name}`", "",
+           f"Capture: `ncu --set full --clock-control none --import-source on -k regex:force_fast -s 3 -c 1 {command}`",
+           f"(report `{os.path.basename(rep)}` stays in gpurun_out/, not committed; numbers taken under ncu are not bench values).",
+           "", "| metric | unit | value |", "|---|---|---|"]
+    for h in WANT:
+        if h in vals:
+            out.append(f"| `{h}` | {vals[h][1]} | {vals[h][0]} |")
+    rd = float(vals["dram__bytes_read.sum"][0]) * UNIT[vals["dram__bytes_read.sum"][1]]
+    wr = float(vals["dram__bytes_write.sum"][0]) * UNIT[vals["dram__bytes_write.sum"][1]]
+    pipe = float(vals["sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active"][0])
+    issue = float(vals["smsp__issue_active.avg.pct_of_peak_sustained_active"][0])
+    out += ["", f"DRAM traffic per launch: {(rd + wr) / 1e6:.2f} MB (read {rd / 1e6:.2f} MB, write {wr / 1e6:.3f} MB). Algorithmic "
+                "bytes: the 16·N-byte position array read once (the partial sums written stay in the 126 MB L2 until the "
+                "finishing kernel reads them). The kernel is FMA-pipe bound; DRAM is idle.",
+            "", f"Reading: FMA pipe busy {pipe:.1f} % of cycles with {issue:.1f} % of issue slots used. What keeps the pipe from 100 % is "
+                "register-file read bandwidth — an FFMA2 with three distinct register pairs takes 3 cycles unless an operand is a "
+                "reuse hit, a MUFU operand fetch takes 1 — see DESIGN.md §4.1 and tools/sass_rf_model.py."]
+    open(os.path.join(PROF, f"{tag}_force_fast_ncu.md"), "w").write("\n".join(out) + "\n")
+    tpath = os.path.join(PROF, "force_kernel_traffic.json")
+    t = json.load(open(tpath)) if os.path.exists(tpath) else {}
+    t[key] = rd + wr
+    t["_note"] = "dram__bytes_read.sum + dram__bytes_write.sum per launch of the force kernel, from ncu --set full captures"
+    json.dump(t, open(tpath, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    tag, lcsv, rep, command = sys.argv[1:5]
+    key = sys.argv[5] if len(sys.argv) > 5 else "n1048576_gpus1"
+    os.makedirs(PROF, exist_ok=True)
+    share = launches(tag, lcsv, command)
+    full(tag, rep, command, key)
+    print(f"force kernel share {share:.4f}; summaries written to profiles/{tag}_*")
