@@ -85,6 +85,15 @@ int nbody_cuda_download_aos(nbody_cuda_t h, void *particles, size_t count);
  * bytes per particle over PCIe. */
 int nbody_cuda_download_positions(nbody_cuda_t h, float *xyz, size_t count);
 
+/* Headless frame of the device-resident positions, RGB8 rows top to bottom into `rgb`
+ * (width*height*3 bytes, host): the picture src/renderers/GlutRenderer.cpp:98-141 draws -- one
+ * orange sphere of radius 2 per particle, one directional light, camera at `camera_distance`
+ * (default there: 800) turned by angle_x then angle_y degrees, gluPerspective(45, w/h, 1, 5000) --
+ * computed by two CUDA kernels (z-buffered disc splat + per-pixel shading).  No graphics API is
+ * involved.  Draws every particle of the replicated position array (all ranks' slices). */
+int nbody_cuda_render_frame(nbody_cuda_t h, int width, int height, float camera_distance, float angle_x_deg,
+                            float angle_y_deg, unsigned char *rgb);
+
 /* n_steps x { force accumulation over all n_total sources for the local targets;
  * v += a*dt; x += v*dt }  -- src/NaiveSimulation.cpp:7-51 / src/MpiNaiveSimulation.cpp:10-141.
  * Device-resident: no host traffic.  With world > 1 this requires attached peers

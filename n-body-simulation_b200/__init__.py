@@ -7,9 +7,9 @@ from ._lib import LIB_PATH, NBodyCudaError, SIGNATURES, build_library, load_libr
 from .simulation import PARTICLE_DTYPE, CudaNaiveSimulation, PinnedParticles, SimParams, slice_counts
 from .sharding import SlotLayout, allgather_slices
 from . import datasets, trajectory
-from .trajectory import TrajectoryReader, TrajectoryWriter, read_restart, write_restart
+from .trajectory import TrajectoryReader, TrajectoryWriter, read_restart, write_ppm, write_restart
 
 __all__ = [
-    "CudaNaiveSimulation", "SimParams", "PARTICLE_DTYPE", "PinnedParticles", "slice_counts", "datasets", "trajectory", "TrajectoryWriter", "TrajectoryReader", "write_restart", "read_restart", "SlotLayout", "allgather_slices",
+    "CudaNaiveSimulation", "SimParams", "PARTICLE_DTYPE", "PinnedParticles", "slice_counts", "datasets", "trajectory", "TrajectoryWriter", "TrajectoryReader", "write_restart", "read_restart", "write_ppm", "SlotLayout", "allgather_slices",
     "NBodyCudaError", "build_library", "load_library", "LIB_PATH", "SIGNATURES",
 ]

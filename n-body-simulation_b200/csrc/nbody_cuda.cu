@@ -552,6 +552,44 @@ int nbody_cuda_download_positions(nbody_cuda_t h, float *xyz, size_t count) {
     return check_fault(h);
 }
 
+int nbody_cuda_render_frame(nbody_cuda_t h, int width, int height, float camera_distance, float angle_x_deg,
+                            float angle_y_deg, unsigned char *rgb) {
+    if (!h) return NBODY_E_INVALID;
+    if (!h->configured) return fail(h, NBODY_E_STATE, "nbody_cuda_render_frame: not configured");
+    if (width < 1 || height < 1 || width > 16384 || height > 16384 || !rgb)
+        return fail(h, NBODY_E_INVALID, "nbody_cuda_render_frame: need 1 <= width, height <= 16384 and a buffer");
+    CU_TRY(h, cudaSetDevice(h->device));
+    const size_t pixels = (size_t)width * height;
+    const size_t bytes = pixels * (sizeof(unsigned long long) + 3) + kMaxWorld * sizeof(int) + 64;
+    int rc = ensure_aos(h, bytes);                 // the boundary staging buffer doubles as frame memory
+    if (rc != NBODY_OK) return rc;
+    unsigned long long *zbuf = reinterpret_cast<unsigned long long *>(h->d_aos);
+    int *d_counts = reinterpret_cast<int *>(zbuf + pixels);
+    unsigned char *d_rgb = reinterpret_cast<unsigned char *>(d_counts + kMaxWorld);
+    CU_TRY(h, cudaMemsetAsync(zbuf, 0xff, pixels * sizeof(unsigned long long), h->stream));
+    CU_TRY(h, cudaMemcpyAsync(d_counts, h->counts, kMaxWorld * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    Camera c;
+    const float deg = 0.017453292519943295f;
+    c.cx = cosf(angle_x_deg * deg); c.sx = sinf(angle_x_deg * deg);
+    c.cy = cosf(angle_y_deg * deg); c.sy = sinf(angle_y_deg * deg);
+    c.distance = camera_distance;
+    c.fy = 0.5f * height / tanf(0.5f * 45.0f * deg);          // gluPerspective(45, w/h, 1, 5000), GlutRenderer.cpp:148
+    c.fx = c.fy;
+    c.radius = 2.0f;                                           // glutSolidSphere(2, 8, 6), GlutRenderer.cpp:131
+    c.znear = 1.0f; c.zfar = 5000.0f;
+    c.width = width; c.height = height;
+    if (h->n_total > 0) {
+        splat_kernel<<<(int)((h->n_slots + kThreads - 1) / kThreads), kThreads, 0, h->stream>>>(
+            h->pos[h->cur], (int)h->n_slots, (int)h->slot_stride, d_counts, c, zbuf);
+        CHECK_LAUNCH(h, "splat_kernel");
+    }
+    shade_kernel<<<(int)((pixels + kThreads - 1) / kThreads), kThreads, 0, h->stream>>>(h->pos[h->cur], c, zbuf, d_rgb);
+    CHECK_LAUNCH(h, "shade_kernel");
+    CU_TRY(h, cudaMemcpyAsync(rgb, d_rgb, pixels * 3, cudaMemcpyDeviceToHost, h->stream));
+    CU_TRY(h, cudaStreamSynchronize(h->stream));
+    return NBODY_OK;
+}
+
 int nbody_cuda_step(nbody_cuda_t h, float G, float dt, float min_r2, int n_steps) {
     if (!h) return NBODY_E_INVALID;
     if (!h->configured) return fail(h, NBODY_E_STATE, "nbody_cuda_step: not configured");

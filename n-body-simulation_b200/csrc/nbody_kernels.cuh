@@ -595,6 +595,95 @@ __global__ void __launch_bounds__(kThreads) energy_kernel(const float4 *__restri
 }
 
 // ---------------------------------------------------------------------------------------------
+// Headless frame of the device positions: what the reference's GLUT viewer draws
+// -- every particle an orange sphere of radius 2 under one directional light, camera pulled back
+// along -z and turned about x then y, 45-degree perspective, near 1, far 5000
+// (src/renderers/GlutRenderer.cpp:19-30,98-141,148) -- as plain compute: no graphics API.
+// Pass 1 splats each sphere's disc into a 64-bit z-buffer with atomicMin on (depth bits, slot), which
+// makes the nearest-surface choice independent of thread order; pass 2 shades the winner per pixel.
+// ---------------------------------------------------------------------------------------------
+struct Camera {
+    float cx, sx, cy, sy;     // cos/sin of the x and y rotation angles
+    float distance;           // translation along -z
+    float fx, fy;             // focal lengths in pixels: (h/2)/tan(fovy/2) both (square pixels)
+    float radius;             // sphere radius in world units
+    float znear, zfar;
+    int width, height;
+};
+
+__device__ __forceinline__ void to_eye(const Camera &c, float x, float y, float z, float &ex, float &ey, float &ez) {
+    const float x1 = x * c.cy + z * c.sy;          // glRotatef(angle_y, 0,1,0)
+    const float z1 = -x * c.sy + z * c.cy;
+    ex = x1;
+    ey = y * c.cx - z1 * c.sx;                      // glRotatef(angle_x, 1,0,0)
+    ez = y * c.sx + z1 * c.cx - c.distance;         // glTranslatef(0,0,-distance); the eye looks down -z
+}
+
+constexpr unsigned long long kEmptyPixel = 0xffffffffffffffffull;
+constexpr int kMaxSplatRadius = 256;    // pixels; larger discs are clamped (a sphere that close fills the view)
+
+__global__ void __launch_bounds__(kThreads) splat_kernel(const float4 *__restrict__ pos, int n_slots, int slot_stride,
+                                                         const int *__restrict__ counts, Camera c,
+                                                         unsigned long long *__restrict__ zbuf) {
+    const int k = blockIdx.x * kThreads + threadIdx.x;
+    if (k >= n_slots) return;
+    const int r = k / slot_stride;
+    if (k - r * slot_stride >= counts[r]) return;            // padding slot
+    const float4 p = pos[k];
+    float ex, ey, ez;
+    to_eye(c, p.x, p.y, p.z, ex, ey, ez);
+    const float depth = -ez;
+    if (!(depth > c.znear) || !(depth < c.zfar)) return;     // centre outside the clip range (also drops NaN)
+    const float px = c.width * 0.5f + c.fx * ex / depth;
+    const float py = c.height * 0.5f - c.fy * ey / depth;
+    float rp = c.fy * c.radius / depth;
+    rp = fminf(rp, (float)kMaxSplatRadius);
+    const int x0 = max(0, (int)floorf(px - rp)), x1 = min(c.width - 1, (int)ceilf(px + rp));
+    const int y0 = max(0, (int)floorf(py - rp)), y1 = min(c.height - 1, (int)ceilf(py + rp));
+    const float inv = 1.0f / fmaxf(rp, 0.5f);                 // sub-pixel spheres still light their own pixel
+    for (int y = y0; y <= y1; ++y)
+        for (int x = x0; x <= x1; ++x) {
+            const float u = ((x + 0.5f) - px) * inv, v = (py - (y + 0.5f)) * inv;
+            const float q = 1.0f - u * u - v * v;
+            const bool centre = (x == (int)floorf(px)) && (y == (int)floorf(py));   // a sphere never vanishes between pixel centres
+            if (q < 0.0f && !centre) continue;
+            const float zs = depth - c.radius * sqrtf(fmaxf(q, 0.0f));   // depth of the sphere surface under this pixel
+            const unsigned long long key = ((unsigned long long)__float_as_uint(fmaxf(zs, 0.0f)) << 32) | (unsigned)k;
+            atomicMin(&zbuf[(size_t)y * c.width + x], key);
+        }
+}
+
+__global__ void __launch_bounds__(kThreads) shade_kernel(const float4 *__restrict__ pos, Camera c,
+                                                         const unsigned long long *__restrict__ zbuf,
+                                                         unsigned char *__restrict__ rgb) {
+    const int i = blockIdx.x * kThreads + threadIdx.x;
+    if (i >= c.width * c.height) return;
+    const unsigned long long key = zbuf[i];
+    unsigned char R = 0, G = 0, B = 0;                        // glClearColor(0,0,0,1)
+    if (key != kEmptyPixel) {
+        const int k = (int)(key & 0xffffffffu);
+        const int x = i % c.width, y = i / c.width;
+        const float4 p = pos[k];
+        float ex, ey, ez;
+        to_eye(c, p.x, p.y, p.z, ex, ey, ez);
+        const float depth = -ez;
+        const float px = c.width * 0.5f + c.fx * ex / depth, py = c.height * 0.5f - c.fy * ey / depth;
+        const float rp = fminf(c.fy * c.radius / depth, (float)kMaxSplatRadius);
+        const float inv = 1.0f / fmaxf(rp, 0.5f);
+        const float u = ((x + 0.5f) - px) * inv, v = (py - (y + 0.5f)) * inv;
+        const float w = sqrtf(fmaxf(0.0f, 1.0f - u * u - v * v));          // eye-space normal (u, v, w)
+        // GL_LIGHT0 at (1,1,1,0) set under an identity modelview: direction fixed in eye space;
+        // ambient 0.3 + default scene ambient 0.2, diffuse 1, GL_COLOR_MATERIAL ambient-and-diffuse
+        const float ndotl = fmaxf(0.0f, (u + v + w) * 0.57735026919f);
+        const float lit = fminf(1.0f, 0.5f + ndotl);
+        R = (unsigned char)(255.0f * lit + 0.5f);                            // glColor3f(1, 0.5, 0)
+        G = (unsigned char)(255.0f * fminf(1.0f, 0.5f * lit) + 0.5f);
+        B = 0;
+    }
+    rgb[3 * i + 0] = R; rgb[3 * i + 1] = G; rgb[3 * i + 2] = B;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Helpers of the allocation-free entry point (nbody_cuda_accel_noalloc): copy the caller's n
 // sources into a tile-padded staging area, and fold the fast kernel's segment partials into
 // accelerations.  Both only ever touch memory handed to them.

@@ -114,3 +114,11 @@ long long CudaNaiveSimulation::kernelLaunches() const {
     for (auto *h : handles_) n += nbody_cuda_launch_count(h);
     return n;
 }
+
+void CudaNaiveSimulation::renderFrame(int width, int height, float camera_distance, float angle_x_deg, float angle_y_deg,
+                                      std::vector<unsigned char> &rgb) {
+    rgb.resize((std::size_t)std::max(width, 0) * std::max(height, 0) * 3);
+    // every device holds all positions; the first one draws
+    check(handles_[0], nbody_cuda_render_frame(handles_[0], width, height, camera_distance, angle_x_deg, angle_y_deg, rgb.data()),
+          "renderFrame");
+}

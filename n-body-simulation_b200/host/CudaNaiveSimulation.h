@@ -49,6 +49,10 @@ public:
     double lastStepMilliseconds();                       // CUDA-event time of the last step call (max over devices)
     void energy(const SimParams &params, double &kinetic, double &potential);
     long long kernelLaunches() const;
+    // Headless picture of the device positions with the reference viewer's camera and markers
+    // (src/renderers/GlutRenderer.cpp:98-148), RGB8 rows top to bottom; CUDA kernels, no graphics API.
+    void renderFrame(int width, int height, float camera_distance, float angle_x_deg, float angle_y_deg,
+                     std::vector<unsigned char> &rgb);
     Mode mode() const { return mode_; }
     int deviceCount() const { return (int)handles_.size(); }
 

@@ -18,6 +18,9 @@
 //   --checkpoint-every K write a trajectory record every K-th step only (default 1, as the reference)
 //   --energy-every K     print the FP64 energy every K steps
 //   --checkpoint FILE    trajectory file name (default simulation_output.bin)
+//   --frame-every K      with --resident: write frame_<step>.ppm every K steps -- the viewer's picture
+//                        (GlutRenderer.cpp:98-148) computed by CUDA kernels, no window, no graphics API
+//   --frame-size WxH     frame size (default 800x600);  --camera D,AX,AY  distance and angles (default 800,0,0)
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -45,7 +48,9 @@ struct Options {
     bool solar = false, write_output = true, resident = false, seeded = false;
     unsigned seed = 0;
     int device = 0, gpus = 1;
-    std::size_t checkpoint_every = 1, energy_every = 0;
+    std::size_t checkpoint_every = 1, energy_every = 0, frame_every = 0;
+    int frame_w = 800, frame_h = 600;
+    float cam_d = 800.f, cam_ax = 0.f, cam_ay = 0.f;
     CudaNaiveSimulation::Mode mode = CudaNaiveSimulation::Mode::Fast;
     SimParams params;
 };
@@ -73,6 +78,9 @@ Options parse(int argc, char **argv) {
         else if (a == "--checkpoint-every") o.checkpoint_every = std::max<std::size_t>(1, std::stoul(next(i)));
         else if (a == "--energy-every") o.energy_every = std::stoul(next(i));
         else if (a == "--checkpoint") o.traj_path = next(i);
+        else if (a == "--frame-every") o.frame_every = std::stoul(next(i));
+        else if (a == "--frame-size") { const std::string v = next(i); std::sscanf(v.c_str(), "%dx%d", &o.frame_w, &o.frame_h); }
+        else if (a == "--camera") { const std::string v = next(i); std::sscanf(v.c_str(), "%f,%f,%f", &o.cam_d, &o.cam_ax, &o.cam_ay); }
         // unknown flags are ignored, as in the reference
     }
     return o;
@@ -136,6 +144,17 @@ int main(int argc, char **argv) {
             if (step % 100 == 0) std::cout << "Step " << step << " / " << opt.steps << " completed\n";
         }
         if (opt.energy_every && (step + 1) % opt.energy_every == 0) report_energy(step + 1);
+        if (opt.frame_every && opt.resident && (step + 1) % opt.frame_every == 0) {
+            std::vector<unsigned char> rgb;
+            algo->renderFrame(opt.frame_w, opt.frame_h, opt.cam_d, opt.cam_ax, opt.cam_ay, rgb);
+            char name[64];
+            std::snprintf(name, sizeof(name), "frame_%06zu.ppm", step + 1);
+            if (FILE *f = std::fopen(name, "wb")) {
+                std::fprintf(f, "P6\n%d %d\n255\n", opt.frame_w, opt.frame_h);
+                std::fwrite(rgb.data(), 1, rgb.size(), f);
+                std::fclose(f);
+            }
+        }
     }
     if (opt.resident) algo->download(sim.particles());       // also drains the GPU before the clock stops
     const auto t1 = std::chrono::high_resolution_clock::now();

@@ -206,6 +206,15 @@ class CudaNaiveSimulation:
         self._ck(self._lib.nbody_cuda_download_positions(self._h, out.ctypes.data_as(C.c_void_p), n))
         return out
 
+    def render_frame(self, width: int = 800, height: int = 600, camera_distance: float = 800.0,
+                     angle_x: float = 0.0, angle_y: float = 0.0) -> np.ndarray:
+        """(height, width, 3) uint8 frame of the device positions with the reference viewer's camera
+        and sphere markers (src/renderers/GlutRenderer.cpp:98-148), rendered by CUDA kernels."""
+        out = np.empty((height, width, 3), np.uint8)
+        self._ck(self._lib.nbody_cuda_render_frame(self._h, width, height, camera_distance, angle_x, angle_y,
+                                                   out.ctypes.data_as(C.c_void_p)))
+        return out
+
     def synchronize(self) -> None:
         self._ck(self._lib.nbody_cuda_synchronize(self._h))
 

@@ -98,3 +98,11 @@ def read_restart(path: str):
         if len(data) != n * rec:
             raise ValueError(f"{path} is truncated")
     return np.frombuffer(data, dtype=PARTICLE_DTYPE).copy(), SimParams(G=G, dt=dt, min_r2=eps), int(step)
+
+
+def write_ppm(path: str, frame: np.ndarray) -> None:
+    """Binary PPM (P6) of an (h, w, 3) uint8 frame, e.g. from CudaNaiveSimulation.render_frame."""
+    f = np.ascontiguousarray(frame, dtype=np.uint8)
+    with open(path, "wb") as out:
+        out.write(b"P6\n%d %d\n255\n" % (f.shape[1], f.shape[0]))
+        out.write(f.tobytes())

@@ -77,3 +77,14 @@ def test_two_gpus_same_trajectory_as_one(app, nb, tmp_path):
     run_app(tmp_path, *common, "--gpus", "2", "--checkpoint", "two.bin", "--out", "two.csv")
     assert open(tmp_path / "one.bin", "rb").read() == open(tmp_path / "two.bin", "rb").read()
     assert open(tmp_path / "two.csv").read().strip().endswith(",2")
+
+
+def test_frames_are_written(app, tmp_path):
+    run_app(tmp_path, "--random", "5000", "--steps", "4", "--seed", "2", "--disable-output", "--resident",
+            "--frame-every", "2", "--frame-size", "160x120", "--camera", "900,20,30", "--out", "f.csv")
+    for step in (2, 4):
+        raw = open(tmp_path / f"frame_{step:06d}.ppm", "rb").read()
+        head = b"P6\n160 120\n255\n"
+        assert raw.startswith(head) and len(raw) == len(head) + 160 * 120 * 3
+        body = np.frombuffer(raw[len(head):], np.uint8).reshape(120, 160, 3)
+        assert (body.sum(axis=2) > 0).mean() > 0.01 and body[..., 2].max() == 0      # orange discs on black
