@@ -85,6 +85,18 @@ int nbody_cuda_download_aos(nbody_cuda_t h, void *particles, size_t count);
  * bytes per particle over PCIe. */
 int nbody_cuda_download_positions(nbody_cuda_t h, float *xyz, size_t count);
 
+/* Fills the configured system with a synthetic particle set generated ON the device, instead of
+ * nbody_cuda_upload_aos: the distributions of NBodySimulation::generatePlummerSphere
+ * (src/Simulation.cpp:173-267; size_a = scale radius, size_b = total mass, < 0 for one per particle)
+ * or ::generateGalaxyDisk (:88-136; size_a = radius, size_b = thickness), drawn from a Philox stream
+ * keyed by (seed, particle index) rather than the reference's mt19937 -- same statistics, not the
+ * same particles.  Every rank of a sharded run calls it with the same arguments and gets the same
+ * global system; no exchange is needed afterwards.  *min_r2_out receives the softening the
+ * reference's generator would set (:131, :195). */
+#define NBODY_GEN_PLUMMER 0
+#define NBODY_GEN_DISK 1
+int nbody_cuda_generate(nbody_cuda_t h, int kind, float size_a, float size_b, float G, unsigned long long seed, float *min_r2_out);
+
 /* Headless frame of the device-resident positions, RGB8 rows top to bottom into `rgb`
  * (width*height*3 bytes, host): the picture src/renderers/GlutRenderer.cpp:98-141 draws -- one
  * orange sphere of radius 2 per particle, one directional light, camera at `camera_distance`

@@ -53,6 +53,7 @@ SIGNATURES = {
     "nbody_cuda_upload_aos": (_i, [_vp, _vp, _sz]),
     "nbody_cuda_download_aos": (_i, [_vp, _vp, _sz]),
     "nbody_cuda_download_positions": (_i, [_vp, _vp, _sz]),
+    "nbody_cuda_generate": (_i, [_vp, _i, _f, _f, _f, C.c_ulonglong, C.POINTER(_f)]),
     "nbody_cuda_render_frame": (_i, [_vp, _i, _i, _f, _f, _f, _vp]),
     "nbody_cuda_step": (_i, [_vp, _f, _f, _f, _i]),
     "nbody_cuda_step_local": (_i, [_vp, _f, _f, _f]),

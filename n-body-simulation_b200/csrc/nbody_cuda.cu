@@ -552,6 +552,53 @@ int nbody_cuda_download_positions(nbody_cuda_t h, float *xyz, size_t count) {
     return check_fault(h);
 }
 
+int nbody_cuda_generate(nbody_cuda_t h, int kind, float size_a, float size_b, float G, unsigned long long seed, float *min_r2_out) {
+    if (!h) return NBODY_E_INVALID;
+    if (!h->configured) return fail(h, NBODY_E_STATE, "nbody_cuda_generate: call nbody_cuda_configure first");
+    if (kind != NBODY_GEN_PLUMMER && kind != NBODY_GEN_DISK) return fail(h, NBODY_E_INVALID, "nbody_cuda_generate: unknown kind");
+    CU_TRY(h, cudaSetDevice(h->device));
+    const size_t n = h->n_total;
+    const double pi = 3.14159265358979323846;
+    float min_r2 = 0.f, total_mass = 0.f;
+    if (kind == NBODY_GEN_PLUMMER) {          // softening: 15 % of the mean spacing inside 2.4 a (Simulation.cpp:186-195)
+        total_mass = (size_b < 0.f) ? (float)n : size_b;
+        const float reff = 2.4f * size_a;
+        const float vol = (float)((4.0 / 3.0) * pi) * reff * reff * reff;
+        const float soft = cbrtf(vol / (float)(n ? n : 1)) * 0.15f;
+        min_r2 = soft * soft;
+    } else {                                   // 10 % of the mean spacing of the disk volume (Simulation.cpp:126-131)
+        const float vol = (float)pi * size_a * size_a * size_b;
+        const float soft = cbrtf(vol / (float)(n ? n : 1)) * 0.1f;
+        min_r2 = soft * soft;
+    }
+    if (min_r2_out) *min_r2_out = min_r2;
+    if (n == 0) return NBODY_OK;
+    const int blocks = (int)((n + kThreads - 1) / kThreads);
+    if ((size_t)3 * blocks > h->energy_cap) {
+        if (h->d_energy) cudaFree(h->d_energy);
+        h->d_energy = nullptr; h->energy_cap = 0;
+        CU_TRY(h, cudaMalloc(&h->d_energy, (size_t)3 * blocks * sizeof(double)));
+        h->energy_cap = (size_t)3 * blocks;
+    }
+    GenArgs a;
+    a.pos = h->pos[h->cur]; a.vel = h->vel; a.vsum = h->d_energy;
+    a.world = h->world; a.slot_stride = (int)h->slot_stride; a.rank = h->rank; a.n_total = (int)n;
+    int d = 0;
+    for (int r = 0; r < kMaxWorld; ++r) { a.counts[r] = h->counts[r]; a.displs[r] = d; d += h->counts[r]; }
+    a.seed = seed; a.a = size_a; a.total_mass = total_mass; a.G = G; a.radius = size_a; a.thickness = size_b;
+    if (kind == NBODY_GEN_PLUMMER) generate_kernel<0><<<blocks, kThreads, 0, h->stream>>>(a);
+    else generate_kernel<1><<<blocks, kThreads, 0, h->stream>>>(a);
+    CHECK_LAUNCH(h, "generate_kernel");
+    if (kind == NBODY_GEN_PLUMMER && h->n_local > 0) {
+        remove_bulk_velocity_kernel<<<(int)((h->n_local + kThreads - 1) / kThreads), kThreads, 0, h->stream>>>(
+            h->vel, (int)h->n_local, h->d_energy, blocks, (double)total_mass);
+        CHECK_LAUNCH(h, "remove_bulk_velocity_kernel");
+    }
+    if (h->n_local > 0) CU_TRY(h, cudaMemsetAsync(h->acc, 0, h->n_local * sizeof(float4), h->stream));
+    h->mass_checked = false;
+    return NBODY_OK;
+}
+
 int nbody_cuda_render_frame(nbody_cuda_t h, int width, int height, float camera_distance, float angle_x_deg,
                             float angle_y_deg, unsigned char *rgb) {
     if (!h) return NBODY_E_INVALID;

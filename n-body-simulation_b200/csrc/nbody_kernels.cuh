@@ -14,6 +14,7 @@
 // zero-mass padding parked far away, so they contribute exactly 0 to every sum.
 #pragma once
 #include <cuda_runtime.h>
+#include <curand_kernel.h>
 #include <stdint.h>
 
 namespace nbody {
@@ -592,6 +593,117 @@ __global__ void __launch_bounds__(kThreads) energy_kernel(const float4 *__restri
         out[2 * blockIdx.x] = K;
         out[2 * blockIdx.x + 1] = U;
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Input generators on the device.  Same distributions as the reference's
+// generatePlummerSphere (src/Simulation.cpp:173-267) and generateGalaxyDisk (:88-136), drawn from
+// a counter-based Philox stream keyed by (seed, global particle index) instead of the reference's
+// sequential mt19937 -- so the particles are NOT the reference's particles (parity tests use the
+// reference's own generators), but every rank can produce any particle independently and
+// identically.  Every rank fills ALL position slots; velocities only for its own slice.
+// ---------------------------------------------------------------------------------------------
+struct GenArgs {
+    float4 *pos;            // current global positions
+    float4 *vel;            // local velocities
+    double *vsum;           // per-CTA partial sums {vx, vy, vz} of ALL particles (bulk-velocity removal)
+    int world, slot_stride, rank;
+    int counts[kMaxWorld], displs[kMaxWorld];
+    int n_total;
+    unsigned long long seed;
+    float a, total_mass, G;             // Plummer: scale radius, total mass
+    float radius, thickness;            // disk
+};
+
+__device__ __forceinline__ float uni(curandStatePhilox4_32_10_t &st, float lo, float hi) {
+    return lo + (hi - lo) * (1.0f - curand_uniform(&st));        // [lo, hi), like uniform_real_distribution
+}
+__device__ __forceinline__ float3 on_sphere(curandStatePhilox4_32_10_t &st, float r) {
+    float x, y, s;                                                // Marsaglia, include/Random.hpp:51-67
+    do { x = uni(st, -1.f, 1.f); y = uni(st, -1.f, 1.f); s = x * x + y * y; } while (s >= 1.0f);
+    const float t = 2.0f * sqrtf(1.0f - s);
+    return make_float3(r * x * t, r * y * t, r * (1.0f - 2.0f * s));
+}
+__device__ __forceinline__ void slot_of_global(const GenArgs &a, int g, int &rank, int &local) {
+    rank = 0;
+    for (int r = a.world - 1; r >= 0; --r)
+        if (a.counts[r] > 0 && g >= a.displs[r]) { rank = r; break; }
+    local = g - a.displs[rank];
+}
+
+template <int kKind>    // 0: Plummer sphere, 1: galaxy disk
+__global__ void __launch_bounds__(kThreads) generate_kernel(const GenArgs a) {
+    __shared__ double red[3][kThreads / 32];
+    const int g = blockIdx.x * kThreads + threadIdx.x;
+    float3 v = make_float3(0.f, 0.f, 0.f);
+    float m = 0.f;
+    if (g < a.n_total) {
+        curandStatePhilox4_32_10_t st;
+        curand_init(a.seed, (unsigned long long)g, 0, &st);
+        float3 p;
+        if (kKind == 0) {
+            m = a.total_mass / (float)a.n_total;
+            const float u = fminf(uni(st, 0.001f, 1.0f), 0.999999f);                 // Simulation.cpp:216 (kept below 1: r stays finite)
+            const float r = a.a / sqrtf(powf(u, -2.0f / 3.0f) - 1.0f);               // :217
+            p = on_sphere(st, r);
+            float q, y;
+            do {                                                                     // :229-242
+                q = uni(st, 0.f, 1.f);
+                y = uni(st, 0.f, 0.1f);
+            } while (!(y < q * q * powf(1.0f - q * q, 3.5f)));
+            const float vesc = sqrtf(2.0f * a.G * a.total_mass / sqrtf(r * r + a.a * a.a));   // :245-246
+            v = on_sphere(st, q * vesc);
+        } else {
+            if (g == 0) {                                                            // :92-98 central mass
+                p = make_float3(0.f, 0.f, 0.f);
+                m = 1.0e6f;
+            } else {
+                const float r = fmaxf(a.radius * sqrtf(uni(st, 0.f, 1.f)), 1e-3f);   // :103
+                const float th = uni(st, 0.f, 6.283185307179586f);
+                const float y = a.thickness * 0.3f * curand_normal(&st);
+                p = make_float3(r * cosf(th), y, r * sinf(th));
+                const float vo = sqrtf(a.G * 1.0e6f / r), disp = 0.1f * vo;          // :112-113
+                v = make_float3(-vo * sinf(th) + disp * curand_normal(&st), 0.5f * disp * curand_normal(&st),
+                                vo * cosf(th) + disp * curand_normal(&st));
+                m = uni(st, 0.5f, 2.0f);                                             // :121
+            }
+        }
+        int r, l;
+        slot_of_global(a, g, r, l);
+        a.pos[r * a.slot_stride + l] = make_float4(p.x, p.y, p.z, m);
+        if (r == a.rank) a.vel[l] = make_float4(v.x, v.y, v.z, 0.f);
+    }
+    // mass-weighted velocity sum of all particles, per CTA, in a fixed order
+    double sx = (double)m * v.x, sy = (double)m * v.y, sz = (double)m * v.z;
+    for (int o = 16; o > 0; o >>= 1) {
+        sx += __shfl_down_sync(0xffffffffu, sx, o);
+        sy += __shfl_down_sync(0xffffffffu, sy, o);
+        sz += __shfl_down_sync(0xffffffffu, sz, o);
+    }
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = sx; red[1][threadIdx.x >> 5] = sy; red[2][threadIdx.x >> 5] = sz; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tx = 0, ty = 0, tz = 0;
+        for (int w = 0; w < kThreads / 32; ++w) { tx += red[0][w]; ty += red[1][w]; tz += red[2][w]; }
+        a.vsum[3 * blockIdx.x] = tx; a.vsum[3 * blockIdx.x + 1] = ty; a.vsum[3 * blockIdx.x + 2] = tz;
+    }
+}
+
+// Plummer only: subtract the bulk velocity (Simulation.cpp:256-265), total momentum / total mass.
+__global__ void __launch_bounds__(kThreads) remove_bulk_velocity_kernel(float4 *vel, int n_local, const double *vsum, int n_blocks,
+                                                                        double total_mass) {
+    __shared__ float bulk[3];
+    if (threadIdx.x == 0) {
+        double tx = 0, ty = 0, tz = 0;
+        for (int b = 0; b < n_blocks; ++b) { tx += vsum[3 * b]; ty += vsum[3 * b + 1]; tz += vsum[3 * b + 2]; }
+        bulk[0] = (float)(tx / total_mass); bulk[1] = (float)(ty / total_mass); bulk[2] = (float)(tz / total_mass);
+    }
+    __syncthreads();
+    const int l = blockIdx.x * kThreads + threadIdx.x;
+    if (l >= n_local) return;
+    float4 v = vel[l];
+    v.x -= bulk[0]; v.y -= bulk[1]; v.z -= bulk[2];
+    vel[l] = v;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -185,6 +185,14 @@ class CudaNaiveSimulation:
             else:
                 self._allgather_positions()
 
+    def generate(self, kind: str, n_total: int, size_a: float, size_b: float, G: float = 1.0, seed: int = 12345) -> float:
+        """Synthetic input generated on the device ("plummer": scale radius, total mass (<0: one per
+        particle); "disk": radius, thickness); returns the min_r2 the reference's generator would set."""
+        self.configure(n_total)
+        eps = C.c_float()
+        self._ck(self._lib.nbody_cuda_generate(self._h, {"plummer": 0, "disk": 1}[kind], size_a, size_b, G, seed, C.byref(eps)))
+        return eps.value
+
     def step(self, params: SimParams, n_steps: int = 1) -> None:
         """n_steps device-resident steps (asynchronous)."""
         if self.world > 1 and self.exchange == "nccl":
