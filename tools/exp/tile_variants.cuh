@@ -119,5 +119,53 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
         for (int k = 0; k < I; ++k) { dx[k] = ndx[k]; dy[k] = ndy[k]; dz[k] = ndz[k]; ri[k] = nri[k]; }
         mcur = mnext;
     }
+#elif VARIANT == 7 || VARIANT == 8 || VARIANT == 10 || VARIANT == 11
+#if VARIANT == 7
+#pragma unroll 4
+#elif VARIANT == 8
+#pragma unroll 3
+#else
+#pragma unroll 2
+#endif
+    for (int q = 0; q < kTileJ / 2; ++q) {
+        const float4 a = sA[q];
+        const float4 b = sB[q];
+        const u64 xj = pack2(a.x, a.y), yj = pack2(a.z, a.w), zj = pack2(b.x, b.y), mj = pack2(b.z, b.w);
+#pragma unroll
+        for (int k = 0; k < I; ++k) {
+            const u64 dx = sub2(xj, xi[k]), dy = sub2(yj, yi[k]), dz = sub2(zj, zi[k]);
+#if VARIANT == 11
+            u64 r2 = fma2(dz, dz, eps2);
+            r2 = fma2(dy, dy, r2);
+            r2 = fma2(dx, dx, r2);
+#else
+            u64 r2 = fma2(dx, dx, eps2);
+            r2 = fma2(dy, dy, r2);
+            r2 = fma2(dz, dz, r2);
+#endif
+            float r2lo, r2hi;
+            unpack2(r2, r2lo, r2hi);
+            const u64 rinv = pack2(rsqrt_approx(r2lo), rsqrt_approx(r2hi));
+            const u64 rinv2 = mul2(rinv, rinv);
+            u64 s = kUnitMass ? mul2(rinv2, rinv) : mul2(mul2(mj, rinv), rinv2);
+            if (kMaskSelf) {
+                float slo, shi;
+                unpack2(s, slo, shi);
+                const int j0 = tile_slot0 + 2 * q, self = self_slot0 + k * kThreads;
+                slo = (j0 == self) ? 0.0f : slo;
+                shi = (j0 + 1 == self) ? 0.0f : shi;
+                s = pack2(slo, shi);
+            }
+#if VARIANT == 10
+            az[k] = fma2(s, dz, az[k]);
+            ay[k] = fma2(s, dy, ay[k]);
+            ax[k] = fma2(s, dx, ax[k]);
+#else
+            ax[k] = fma2(dx, s, ax[k]);
+            ay[k] = fma2(dy, s, ay[k]);
+            az[k] = fma2(dz, s, az[k]);
+#endif
+        }
+    }
 #endif
 }
