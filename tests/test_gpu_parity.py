@@ -389,3 +389,26 @@ def test_fast_mode_against_gpu_fp64_at_config3_size(nb, fast, fp64):
     e = rel_err(a, b)
     print("fast vs fp64 at N=262144: max %.3g median %.3g" % (e.max(), np.median(e)))
     assert np.median(e) < 2e-6 and e.max() < 5e-5
+
+
+def test_config5_size_round_trip_and_limits(nb, fast):
+    """BASELINE configs[4] size through the boundary (no stepping: 1.8e13 interactions per step belong
+    to the 8-GPU run): 4,194,304 particles up, back, and as a trajectory record; sizes past the slot
+    index range are refused with a message, not attempted."""
+    n = 4194304
+    rng = np.random.default_rng(3)
+    p = np.zeros(n, nb.PARTICLE_DTYPE)
+    p["position"] = rng.standard_normal((n, 3)).astype(np.float32)
+    p["velocity"] = rng.standard_normal((n, 3)).astype(np.float32)
+    p["mass"] = rng.uniform(0.5, 2.0, n).astype(np.float32)
+    fast.upload(p)
+    out = np.zeros_like(p)
+    fast.download(out)
+    for k in ("position", "velocity", "mass"):
+        assert same_bits(np.ascontiguousarray(out[k]), np.ascontiguousarray(p[k])), k
+    assert same_bits(fast.download_positions(), np.ascontiguousarray(p["position"]))
+    lib = nb.load_library()
+    assert lib.nbody_cuda_configure(fast._h, (1 << 30) + 1, 0, 1) == -1
+    assert b"2^30" in lib.nbody_cuda_last_error(fast._h)
+    assert lib.nbody_cuda_configure(fast._h, 100, 3, 2) == -1           # rank >= world
+    fast.n_total = None                                                  # the handle is reconfigured by the next upload
