@@ -19,7 +19,6 @@ import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -189,7 +188,6 @@ def run_reference(args):
 # our arm
 # ------------------------------------------------------------------------------------------------
 def run_ours(args):
-    import numpy as np
     import torch
 
     import nbody_b200 as nb

@@ -22,7 +22,7 @@ from dataclasses import dataclass
 import numpy as np
 
 from . import _lib
-from ._lib import NBodyCudaError
+from ._lib import NBodyCudaError  # noqa: F401  (re-exported)
 from .sharding import SlotLayout, allgather_slices
 
 # include/Particle.hpp:53-59
@@ -101,7 +101,6 @@ class CudaNaiveSimulation:
         _lib.check(self._lib, None, code)
         self._h = h
         self.n_total = None
-        self._peers_ready = False
         self._pos_tensors = {}
         self._ext_stream = None
 
@@ -133,7 +132,6 @@ class CudaNaiveSimulation:
             return
         self._ck(self._lib.nbody_cuda_configure(self._h, n_total, self.rank, self.world))
         self.n_total = n_total
-        self._peers_ready = False
         self._pos_tensors = {}
         if self.world > 1 and self.exchange == "p2p":
             self._attach_peers()
@@ -155,7 +153,6 @@ class CudaNaiveSimulation:
             buf = (C.c_ubyte * _lib.PEER_HANDLE_BYTES).from_buffer_copy(t)
             self._ck(self._lib.nbody_cuda_peer_attach(self._h, r, buf))
         self._dist.barrier(group=self.group)
-        self._peers_ready = True
 
     def _allgather_positions(self) -> None:
         """NCCL baseline: in-place all-gather of the current position array on the handle's stream."""

@@ -2,8 +2,6 @@
 generators' distributions (src/Simulation.cpp:88-136, :173-267) from a different random stream, so
 the checks are statistical -- against the reference's own generator where the compiled reference
 is available, else against this repo's NumPy generator -- plus determinism and slice-independence."""
-import ctypes as C
-
 import numpy as np
 import pytest
 

@@ -42,6 +42,10 @@ __global__ void __launch_bounds__(256) k(const float* __restrict__ in, float* ou
                 if (MODE==5) { facc[i]=ffma(facc[i],fs,fb); facc[i+K]=ffma(facc[i+K],fs,fb); }
                 if (MODE==6) { acc[i]=fma2(x[i], x[i], acc[i]); if ((r*K+i)%6==0) mu[(i>>1)&3] = rsq(mu[(i>>1)&3]); }
                 if (MODE==7) acc[i]=fma2(x[i&3], y[(i+r)&3], acc[i]);
+                if (MODE==8) acc[i]=mul2(acc[i], acc[i]);
+                if (MODE==9) { acc[i]=mul2(acc[i], acc[i]); if ((r*K+i)%6==0) mu[(i>>1)&3] = rsq(mu[(i>>1)&3]); }
+                if (MODE==10) { acc[i]=fma2(x[i], x[i], acc[i]); if ((r*K+i)%3==0) mu[(i>>1)&3] = rsq(mu[(i>>1)&3]); }
+                if (MODE==11) { acc[i]=mul2(acc[i], acc[i]); if ((r*K+i)%3==0) mu[(i>>1)&3] = rsq(mu[(i>>1)&3]); }
             }
         }
     }
@@ -72,5 +76,9 @@ int main(){
     run<5>("ffma acc=acc*s+b", in,out,sm);
     run<6>("fma2 2-distinct + 2 MUFU per 12", in,out,sm);
     run<7>("fma2 acc=x[i&3]*y[(i+r)&3]+acc", in,out,sm);
+    run<8>("mul2 acc=acc*acc (1 pair)", in,out,sm);
+    run<9>("mul2 1-pair + 2 MUFU per 12", in,out,sm);
+    run<10>("fma2 2-distinct + 4 MUFU per 12", in,out,sm);
+    run<11>("mul2 1-pair + 4 MUFU per 12", in,out,sm);
     return 0;
 }

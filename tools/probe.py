@@ -1,7 +1,6 @@
 """Quick on-GPU probe: FMA-pipe micro-benchmark and force-kernel throughput at a few sizes."""
-import sys, os, time
+import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np
 import nbody_b200 as nb
 
 sim = nb.CudaNaiveSimulation(mode="fast")

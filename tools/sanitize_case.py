@@ -4,8 +4,6 @@ import ctypes as C
 import os
 import sys
 
-import numpy as np
-
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import nbody_b200 as nb
 
