@@ -11,6 +11,8 @@
  *   - every `int` function returns 0 on success and a negative NBODY_E_* code on failure; the
  *     text of the last failure is at nbody_cuda_last_error(handle) (NULL handle: the last
  *     failure of nbody_cuda_create on this thread).  Nothing throws, nothing calls exit().
+ *   - every call on a handle makes the handle's device the calling thread's current CUDA device
+ *     (cudaSetDevice) and leaves it so.
  *   - a handle is bound to ONE device and ONE host thread at a time (the reference calls
  *     computeStep from exactly one thread: src/Simulation.cpp:269-271).
  *   - `particles` is the reference's 40-byte array-of-structures record
