@@ -129,6 +129,7 @@ size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 // words of the 64-word flag block that follows the position arrays
 constexpr int kFaultWord = 32;    // flags[0..15]: barrier counters, flags[32]: barrier fault
 constexpr int kMassInfoWord = 40; // flags[40]: masses differ, flags[41]: bits of the common mass
+constexpr int kDoneWord = 48;     // flags[48]: CTA ticket counter of the finishing kernel
 
 void slice_of(size_t n, int world, int r, size_t *begin, size_t *count) {
     // counts[r] = n/P + (r < n%P), displs = prefix sum: src/apps/headless_main.cpp:249-259
@@ -315,17 +316,20 @@ unsigned *peer_flags_of(nbody_cuda_t h, int r) {
     return reinterpret_cast<unsigned *>(reinterpret_cast<float4 *>(h->peer_block[r]) + 2 * h->n_slots);
 }
 
-// signal every peer, then wait for every peer (device-side; nothing blocks the host)
-int launch_barrier(nbody_cuda_t h) {
-    h->barrier_seq++;
-    SignalArgs s;
-    s.seq = h->barrier_seq; s.my_rank = h->rank;
-    int k = 0;
-    for (int r = 0; r < h->world; ++r)
-        if (r != h->rank) s.peer_flags[k++] = peer_flags_of(h, r);
-    s.n_peers = k;
-    signal_kernel<<<1, 32, 0, h->stream>>>(s);
-    CHECK_LAUNCH(h, "signal_kernel");
+// signal every peer (unless the finishing kernel of this step already did), then wait for every
+// peer (device-side; nothing blocks the host)
+int launch_barrier(nbody_cuda_t h, bool already_signalled) {
+    if (!already_signalled) {
+        h->barrier_seq++;
+        SignalArgs s;
+        s.seq = h->barrier_seq; s.my_rank = h->rank;
+        int k = 0;
+        for (int r = 0; r < h->world; ++r)
+            if (r != h->rank) s.peer_flags[k++] = peer_flags_of(h, r);
+        s.n_peers = k;
+        signal_kernel<<<1, 32, 0, h->stream>>>(s);
+        CHECK_LAUNCH(h, "signal_kernel");
+    }
     WaitArgs w;
     w.seq = h->barrier_seq; w.my_rank = h->rank; w.world = h->world; w.flags = h->flags;
     w.fault = h->flags + kFaultWord; w.timeout_ns = h->barrier_timeout_ns;
@@ -343,7 +347,14 @@ int launch_finish(nbody_cuda_t h, float G, float dt, bool publish) {
     a.G = G; a.dt = dt; a.plan = h->plan;
     a.n_peers = 0;
     a.mass_info = h->flags + kMassInfoWord;
+    a.done_counter = h->flags + kDoneWord; a.signal_seq = 0; a.my_rank = h->rank;
     if (publish) fill_peer_ptrs(h, h->cur ^ 1, a.peer_next, &a.n_peers);
+    if (a.n_peers > 0) {                      // this launch also raises our step counter at the peers
+        a.signal_seq = ++h->barrier_seq;
+        int k = 0;
+        for (int r = 0; r < h->world; ++r)
+            if (r != h->rank && h->attached[r]) a.peer_flags[k++] = peer_flags_of(h, r);
+    }
     const int grid = (int)((h->n_local + kThreads - 1) / kThreads);
     if (h->mode != NBODY_MODE_FAST) finish_kernel<false><<<grid, kThreads, 0, h->stream>>>(a);
     else finish_kernel<true><<<grid, kThreads, 0, h->stream>>>(a);
@@ -354,12 +365,14 @@ int launch_finish(nbody_cuda_t h, float G, float dt, bool publish) {
 int one_step(nbody_cuda_t h, float G, float dt, float min_r2, bool exchange) {
     int rc;
     if ((rc = ensure_mass_info(h)) != NBODY_OK) return rc;
+    bool signalled = false;
     if (h->n_local > 0) {
         if ((rc = launch_force(h, G, min_r2)) != NBODY_OK) return rc;
         if ((rc = launch_finish(h, G, dt, exchange)) != NBODY_OK) return rc;
+        signalled = exchange && h->world > 1;       // the finishing kernel published and signalled
     }
     if (exchange && h->world > 1)
-        if ((rc = launch_barrier(h)) != NBODY_OK) return rc;
+        if ((rc = launch_barrier(h, signalled)) != NBODY_OK) return rc;
     h->cur ^= 1;
     return NBODY_OK;
 }
@@ -861,7 +874,7 @@ int nbody_cuda_exchange(nbody_cuda_t h) {
         publish_kernel<<<(int)((h->n_local + kThreads - 1) / kThreads), kThreads, 0, h->stream>>>(a);
         CHECK_LAUNCH(h, "publish_kernel");
     }
-    return launch_barrier(h);
+    return launch_barrier(h, false);
 }
 
 int nbody_cuda_host_alloc(void **ptr, size_t bytes) {

@@ -365,41 +365,64 @@ struct FinishArgs {
     int n_peers;
     float4 *peer_next[kMaxWorld];
     const unsigned *mass_info;   // as ForceArgs::mass_info
+    // cross-GPU hand-over, fused into this kernel: the CTA that finishes last raises this rank's
+    // step counter in every peer's flag block once all stores above are system-visible
+    unsigned *done_counter;      // own block; 0 between launches
+    unsigned *peer_flags[kMaxWorld];
+    unsigned signal_seq;
+    int my_rank;
 };
 
 template <bool kFromPartials>
 __global__ void __launch_bounds__(kThreads) finish_kernel(const FinishArgs a) {
     const int l = blockIdx.x * kThreads + threadIdx.x;
-    if (l >= a.n_local) return;
-    float4 acc;
-    if (kFromPartials) {
-        const int t = l / a.TI, r = l - t * a.TI;
-        const int c0 = plan_owner(a.plan, (long long)t * a.plan.n_jtiles);
-        const int c1 = plan_owner(a.plan, (long long)(t + 1) * a.plan.n_jtiles - 1);
-        float sx = 0.0f, sy = 0.0f, sz = 0.0f;
-        for (int c = c0; c <= c1; ++c) {
-            const float4 p = a.partial[(size_t)(c + t) * a.TI + r];
-            sx += p.x; sy += p.y; sz += p.z;
+    if (l < a.n_local) {
+        float4 acc;
+        if (kFromPartials) {
+            const int t = l / a.TI, r = l - t * a.TI;
+            const int c0 = plan_owner(a.plan, (long long)t * a.plan.n_jtiles);
+            const int c1 = plan_owner(a.plan, (long long)(t + 1) * a.plan.n_jtiles - 1);
+            float sx = 0.0f, sy = 0.0f, sz = 0.0f;
+            for (int c = c0; c <= c1; ++c) {
+                const float4 p = a.partial[(size_t)(c + t) * a.TI + r];
+                sx += p.x; sy += p.y; sz += p.z;
+            }
+            float scale = a.G;
+            if (a.mass_info != nullptr && a.mass_info[0] == 0u) scale = a.G * __uint_as_float(a.mass_info[1]);
+            acc = make_float4(scale * sx, scale * sy, scale * sz, 0.0f);
+            a.acc[l] = acc;
+        } else {
+            acc = a.acc[l];
         }
-        float scale = a.G;
-        if (a.mass_info != nullptr && a.mass_info[0] == 0u) scale = a.G * __uint_as_float(a.mass_info[1]);
-        acc = make_float4(scale * sx, scale * sy, scale * sz, 0.0f);
-        a.acc[l] = acc;
-    } else {
-        acc = a.acc[l];
+        const int slot = a.i_slot_begin + l;
+        float4 p = a.pos_cur[slot];
+        float4 v = a.vel[l];
+        v.x = __fadd_rn(v.x, __fmul_rn(acc.x, a.dt));
+        v.y = __fadd_rn(v.y, __fmul_rn(acc.y, a.dt));
+        v.z = __fadd_rn(v.z, __fmul_rn(acc.z, a.dt));
+        p.x = __fadd_rn(p.x, __fmul_rn(v.x, a.dt));
+        p.y = __fadd_rn(p.y, __fmul_rn(v.y, a.dt));
+        p.z = __fadd_rn(p.z, __fmul_rn(v.z, a.dt));
+        a.vel[l] = v;
+        a.pos_next[slot] = p;
+        for (int q = 0; q < a.n_peers; ++q) a.peer_next[q][slot] = p;      // NVLink stores into each peer's array
     }
-    const int slot = a.i_slot_begin + l;
-    float4 p = a.pos_cur[slot];
-    float4 v = a.vel[l];
-    v.x = __fadd_rn(v.x, __fmul_rn(acc.x, a.dt));
-    v.y = __fadd_rn(v.y, __fmul_rn(acc.y, a.dt));
-    v.z = __fadd_rn(v.z, __fmul_rn(acc.z, a.dt));
-    p.x = __fadd_rn(p.x, __fmul_rn(v.x, a.dt));
-    p.y = __fadd_rn(p.y, __fmul_rn(v.y, a.dt));
-    p.z = __fadd_rn(p.z, __fmul_rn(v.z, a.dt));
-    a.vel[l] = v;
-    a.pos_next[slot] = p;
-    for (int q = 0; q < a.n_peers; ++q) a.peer_next[q][slot] = p;
+    if (a.n_peers > 0) {
+        // the barrier orders the CTA's peer stores before thread 0, whose system-scope fence is
+        // cumulative over them (one fence per CTA, not per thread); it then takes a ticket, and
+        // whoever draws the last ticket knows every CTA is past its fence and signals the peers
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            const unsigned ticket = atomicAdd(a.done_counter, 1u);
+            if (ticket == gridDim.x - 1) {
+                atomicExch(a.done_counter, 0u);
+                __threadfence_system();
+                for (int q = 0; q < a.n_peers; ++q)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flags[q] + a.my_rank), "r"(a.signal_seq) : "memory");
+            }
+        }
+    }
 }
 
 // Decides whether all real particles carry the same mass (bitwise): info[0] = 1 if not,
