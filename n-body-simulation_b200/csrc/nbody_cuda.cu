@@ -57,6 +57,7 @@ struct nbody_cuda {
     unsigned *flags = nullptr;
     int cur = 0;
     bool mass_checked = false;   // mass_info (flags[40..41]) describes the uploaded masses
+    int mass_state = -1;         // host copy of the flag: -1 not read yet, 0 unequal masses, 1 all equal
     unsigned barrier_seq = 0;
     unsigned long long barrier_timeout_ns = 30ull * 1000000000ull;
 
@@ -85,7 +86,8 @@ struct nbody_cuda {
     // that small systems are not bound by launch latency
     cudaGraphExec_t step_graph = nullptr;
     float graph_G = 0.f, graph_dt = 0.f, graph_eps2 = 0.f;
-    int graph_parity = 0;
+    int graph_parity = 0, graph_mass_state = -1;
+    long long graph_launches = 0;   // kernels in one replay
     bool capturing = false;
 
     // profiling
@@ -121,7 +123,7 @@ int fail(nbody_cuda_t h, int code, const std::string &msg) {
         cudaError_t e__ = cudaGetLastError();                                                    \
         if (e__ != cudaSuccess)                                                                  \
             return fail((h), NBODY_E_CUDA, std::string("launch of ") + name + ": " + cudaGetErrorString(e__)); \
-        if (!(h)->capturing) (h)->launches++;                                                    \
+        if ((h)->capturing) (h)->graph_launches++; else (h)->launches++;                         \
     } while (0)
 
 size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -223,6 +225,18 @@ int ensure_aos(nbody_cuda_t h, size_t bytes) {
     return NBODY_OK;
 }
 
+template <bool kUnit>
+void launch_fast_variant(int I, int grid, cudaStream_t st, const ForceArgs &a) {
+    switch (I) {
+        case 8: force_fast_kernel<8, kUnit><<<grid, kThreads, 0, st>>>(a); break;
+        case 7: force_fast_kernel<7, kUnit><<<grid, kThreads, 0, st>>>(a); break;
+        case 6: force_fast_kernel<6, kUnit><<<grid, kThreads, 0, st>>>(a); break;
+        case 4: force_fast_kernel<4, kUnit><<<grid, kThreads, 0, st>>>(a); break;
+        case 2: force_fast_kernel<2, kUnit><<<grid, kThreads, 0, st>>>(a); break;
+        default: force_fast_kernel<1, kUnit><<<grid, kThreads, 0, st>>>(a); break;
+    }
+}
+
 // Masses never change on the device, so one look after each upload (and after the exchange that
 // completes the replicated array) tells the fast kernel whether it may drop m_j from its loop.
 int ensure_mass_info(nbody_cuda_t h) {
@@ -277,15 +291,16 @@ int launch_force(nbody_cuda_t h, float G, float min_r2) {
         a.n_local = (int)h->n_local; a.i_slot_begin = (int)(h->rank * h->slot_stride);
         a.eps2 = min_r2; a.plan = h->plan;
         a.mass_info = h->flags + kMassInfoWord;
-        switch (h->targets_per_thread) {
-            case 8: force_fast_kernel<8><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
-            case 7: force_fast_kernel<7><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
-            case 6: force_fast_kernel<6><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
-            case 4: force_fast_kernel<4><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
-            case 2: force_fast_kernel<2><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
-            default: force_fast_kernel<1><<<h->plan.grid, kThreads, 0, h->stream>>>(a); break;
+        // until the host has seen the mass flag (first synchronising call after an upload) both loops
+        // are enqueued and the one that does not apply exits immediately
+        if (h->mass_state != 0) {
+            launch_fast_variant<true>(h->targets_per_thread, h->plan.grid, h->stream, a);
+            CHECK_LAUNCH(h, "force_fast_kernel<uniform mass>");
         }
-        CHECK_LAUNCH(h, "force_fast_kernel");
+        if (h->mass_state != 1) {
+            launch_fast_variant<false>(h->targets_per_thread, h->plan.grid, h->stream, a);
+            CHECK_LAUNCH(h, "force_fast_kernel<general>");
+        }
     }
     if (h->profile_force) CU_TRY(h, cudaEventRecord(e1, h->stream));
     return NBODY_OK;
@@ -301,8 +316,20 @@ void fill_peer_ptrs(nbody_cuda_t h, int which_pos, float4 **out, int *n) {
 }
 
 
+// After a stream synchronise: pick up the mass flag so that later steps enqueue only the loop
+// that applies.
+void learn_mass_state(nbody_cuda_t h) {
+    if (h->mode != NBODY_MODE_FAST || !h->mass_checked || h->mass_state >= 0 || !h->flags) return;
+    unsigned differ = 0;
+    if (cudaMemcpy(&differ, h->flags + kMassInfoWord, sizeof(differ), cudaMemcpyDeviceToHost) == cudaSuccess)
+        h->mass_state = differ ? 0 : 1;
+    else
+        cudaGetLastError();
+}
+
 // Reports a barrier that gave up (a peer never arrived).  Called after a stream synchronise.
 int check_fault(nbody_cuda_t h) {
+    learn_mass_state(h);
     if (h->world == 1 || !h->flags) return NBODY_OK;
     unsigned f = 0;
     CU_TRY(h, cudaMemcpy(&f, h->flags + kFaultWord, sizeof(f), cudaMemcpyDeviceToHost));
@@ -485,6 +512,7 @@ int nbody_cuda_configure(nbody_cuda_t h, size_t n_total, int rank, int world) {
     h->cur = 0;
     h->barrier_seq = 0;
     h->mass_checked = false;
+    h->mass_state = -1;
     // everything is padding until particles arrive
     const int total = (int)(2 * n_slots);
     pad_kernel<<<(total + 255) / 256, 256, 0, h->stream>>>(h->pos[0], 0, total);
@@ -525,6 +553,7 @@ int nbody_cuda_upload_aos(nbody_cuda_t h, const void *particles, size_t count) {
                                                        (int)(h->rank * h->slot_stride), h->pos[h->cur], h->vel, h->acc);
     CHECK_LAUNCH(h, "aos_to_soa_kernel");
     h->mass_checked = false;
+    h->mass_state = -1;
     return NBODY_OK;
 }
 
@@ -609,6 +638,7 @@ int nbody_cuda_generate(nbody_cuda_t h, int kind, float size_a, float size_b, fl
     }
     if (h->n_local > 0) CU_TRY(h, cudaMemsetAsync(h->acc, 0, h->n_local * sizeof(float4), h->stream));
     h->mass_checked = false;
+    h->mass_state = -1;
     return NBODY_OK;
 }
 
@@ -662,13 +692,15 @@ int nbody_cuda_step(nbody_cuda_t h, float G, float dt, float min_r2, int n_steps
     if (use_graph) {
         int rc = ensure_mass_info(h);           // outside the capture: it runs once per upload
         if (rc != NBODY_OK) return rc;
-        if (h->step_graph && (h->graph_G != G || h->graph_dt != dt || h->graph_eps2 != min_r2 || h->graph_parity != h->cur))
+        if (h->step_graph && (h->graph_G != G || h->graph_dt != dt || h->graph_eps2 != min_r2 || h->graph_parity != h->cur ||
+                              h->graph_mass_state != h->mass_state))
             drop_graph(h);
         if (!h->step_graph) {
             // two steps = one full turn of the double-buffered positions, so the graph can be replayed
             cudaGraph_t g = nullptr;
             CU_TRY(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
             h->capturing = true;
+            h->graph_launches = 0;
             rc = one_step(h, G, dt, min_r2, true);
             if (rc == NBODY_OK) rc = one_step(h, G, dt, min_r2, true);
             h->capturing = false;
@@ -679,13 +711,14 @@ int nbody_cuda_step(nbody_cuda_t h, float G, float dt, float min_r2, int n_steps
             cudaGraphDestroy(g);
             CU_TRY(h, e);
             h->graph_G = G; h->graph_dt = dt; h->graph_eps2 = min_r2; h->graph_parity = h->cur;
+            h->graph_mass_state = h->mass_state;
         }
     }
     CU_TRY(h, cudaEventRecord(h->ev_begin, h->stream));
     if (use_graph) {
         for (; done + 2 <= n_steps; done += 2) {
             CU_TRY(h, cudaGraphLaunch(h->step_graph, h->stream));
-            h->launches += 4;                   // force + finish, twice
+            h->launches += h->graph_launches;
         }
     }
     for (; done < n_steps; ++done) {
@@ -1033,14 +1066,7 @@ extern "C" int nbody_cuda_accel_noalloc(const void *d_positions, void *d_acceler
     ForceArgs a;
     a.pos = stage; a.partial = partial; a.n_local = (int)n; a.i_slot_begin = 0; a.eps2 = min_r2; a.plan = plan;
     a.mass_info = nullptr;
-    switch (I) {
-        case 8: force_fast_kernel<8><<<plan.grid, kThreads, 0, st>>>(a); break;
-        case 7: force_fast_kernel<7><<<plan.grid, kThreads, 0, st>>>(a); break;
-        case 6: force_fast_kernel<6><<<plan.grid, kThreads, 0, st>>>(a); break;
-        case 4: force_fast_kernel<4><<<plan.grid, kThreads, 0, st>>>(a); break;
-        case 2: force_fast_kernel<2><<<plan.grid, kThreads, 0, st>>>(a); break;
-        default: force_fast_kernel<1><<<plan.grid, kThreads, 0, st>>>(a); break;
-    }
+    launch_fast_variant<false>(I, plan.grid, st, a);      // mass_info is NULL: the general loop
     if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(err, err_len, NBODY_E_CUDA, "launch of force_fast_kernel", e);
     reduce_partials_kernel<<<(int)((n + kThreads - 1) / kThreads), kThreads, 0, st>>>(partial, (int)n, kThreads * I, G, plan,
                                                                                       (float4 *)d_accelerations);

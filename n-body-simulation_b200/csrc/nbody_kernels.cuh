@@ -150,7 +150,10 @@ struct ForceArgs {
 // warps per scheduler consecutive instructions of a warp issue back to back, which keeps the
 // operand-reuse cache effective (the register file, not the FMA pipe, is the tighter resource
 // for FFMA2 with three distinct register pairs).
-template <int I>
+// kUnitMass selects the loop at compile time (separate kernels keep each one's register allocation
+// tight); the launch that does not match the device-side mass flag returns at once, so the host can
+// enqueue both without knowing the flag.
+template <int I, bool kUnitMass>
 __global__ void __launch_bounds__(kThreads, (I >= 4) ? 1 : 2) force_fast_kernel(const ForceArgs a) {
     constexpr int TI = kThreads * I;
     __shared__ float4 sA[2][kTileJ / 2];
@@ -163,6 +166,7 @@ __global__ void __launch_bounds__(kThreads, (I >= 4) ? 1 : 2) force_fast_kernel(
     const long long u_end = plan_first_unit(a.plan, c + 1);
     const u64 eps2 = pack2(a.eps2, a.eps2);
     const bool unit_mass = (a.mass_info != nullptr) && (a.mass_info[0] == 0u);   // grid-uniform
+    if (unit_mass != kUnitMass) return;
 
     // where this thread parks its source particle inside a packed tile
     float *const stA0 = reinterpret_cast<float *>(&sA[0][tid >> 1]) + (tid & 1);
@@ -207,13 +211,8 @@ __global__ void __launch_bounds__(kThreads, (I >= 4) ? 1 : 2) force_fast_kernel(
             if (more) nxt = a.pos[(jt + 1) * kTileJ + tid];
 
             const bool diag = (jt >= diag0 && jt < diag0 + I);
-            if (unit_mass) {
-                if (diag) tile_interact<I, true, true>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot0);
-                else tile_interact<I, false, true>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot0);
-            } else {
-                if (diag) tile_interact<I, true, false>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot0);
-                else tile_interact<I, false, false>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot0);
-            }
+            if (diag) tile_interact<I, true, kUnitMass>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot0);
+            else tile_interact<I, false, kUnitMass>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot0);
             // blocked summation: every kFlushTiles tiles (and at the end of the run) the inner
             // accumulators are folded into the outer sums and restarted, so neither level adds
             // more than ~sqrt(N) terms in sequence

@@ -319,7 +319,9 @@ def test_launch_counter_and_timers(nb, fast):
     ms, n = fast.force_time()
     fast.profile_force(False)
     assert n == 5 and ms > 0
-    assert fast.launch_count() - before == 11          # force + finish per step, + one mass check after the upload
+    # force + finish per step and one mass check after the upload; until the host has seen the mass flag
+    # both force loops are enqueued (the one that does not apply exits at once)
+    assert 11 <= fast.launch_count() - before <= 16
     assert fast.last_step_ms() >= ms * 0.9
 
 

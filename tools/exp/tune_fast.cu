@@ -35,10 +35,11 @@ int main(int argc, char** argv) {
         cudaMemcpy(info, hi, 8, cudaMemcpyHostToDevice);
         ForceArgs a; a.pos = pos; a.partial = partial; a.n_local = n; a.i_slot_begin = 0; a.eps2 = 0.01f; a.plan = p; a.mass_info = info;
         cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-        force_fast_kernel<I><<<p.grid, 256>>>(a); cudaDeviceSynchronize();
+        auto launch = [&]() { if (unit) force_fast_kernel<I, true><<<p.grid, 256>>>(a); else force_fast_kernel<I, false><<<p.grid, 256>>>(a); };
+        launch(); cudaDeviceSynchronize();
         float best = 1e30f;
-        for (int r = 0; r < 3; ++r) { cudaEventRecord(e0); force_fast_kernel<I><<<p.grid, 256>>>(a); cudaEventRecord(e1); cudaEventSynchronize(e1); float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms; }
-        cudaFuncAttributes fa; cudaFuncGetAttributes(&fa, force_fast_kernel<I>);
+        for (int r = 0; r < 3; ++r) { cudaEventRecord(e0); launch(); cudaEventRecord(e1); cudaEventSynchronize(e1); float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms; }
+        cudaFuncAttributes fa; if (unit) cudaFuncGetAttributes(&fa, force_fast_kernel<I, true>); else cudaFuncGetAttributes(&fa, force_fast_kernel<I, false>);
         std::vector<float4> out(8); cudaMemcpy(out.data(), partial, 8 * sizeof(float4), cudaMemcpyDeviceToHost);
         printf("variant %d I=%d %s n=%d regs=%d: %.3f ms  %.4e int/s  %.1f%% of 74.45 TF  (check %.6e)\n", VARIANT, I, unit ? "unit" : "general", n, fa.numRegs, best,
                (double)n * n / (best * 1e-3), (double)n * n / (best * 1e-3) * 20 / 74.45e12 * 100, out[3].x);
