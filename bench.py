@@ -245,12 +245,12 @@ def run_ours(args):
     local = p[lo:lo + cnt].copy()
     sim.upload(local, n_total=n)
     sim.synchronize()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()          # before the warm-up: nvidia-smi's own start-up must not land in the timed region
     for s in range(args.warmup):
         sim.step(params, 1)
     sim.synchronize()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
     launches0 = sim.launch_count()
     sim.profile_force(True)
     sim.force_time(reset=True)
