@@ -251,6 +251,15 @@ def run_ours(args):
     for s in range(args.warmup):
         sim.step(params, 1)
     sim.synchronize()
+    # short steps (small N): W steps are over in milliseconds, before the SM clock has left idle; keep
+    # warming up (untimed) until half a second of device work has been done
+    extra_warmup = 0
+    per_step_ms = max(sim.last_step_ms(), 1e-3)
+    if per_step_ms * args.warmup < 500.0:
+        extra_warmup = int(min(20000, (500.0 - per_step_ms * args.warmup) / per_step_ms))
+        if extra_warmup > 0:
+            sim.step(params, extra_warmup)
+            sim.synchronize()
     launches0 = sim.launch_count()
     sim.profile_force(True)
     sim.force_time(reset=True)
@@ -342,6 +351,7 @@ def run_ours(args):
             "config": {"workload": f"{args.workload}: {mirrors}", "n": n, "generator": gen, "G": 1.0, "dt": 0.5,
                        "min_r2": eps, "mode": args.mode, "exchange": args.exchange if world > 1 else "none",
                        "parallelism": f"i-slice x{world}", "l2": "flushed between steps (160 MiB memset, inside the timed region)",
+                       "extra_warmup_steps": extra_warmup,
                        "plan": plan},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches), "roofline": roofline, "cpu_baseline": cpu,
         }
