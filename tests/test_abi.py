@@ -62,3 +62,40 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert "liboracle" not in src and "libnbody_ref" not in src, f
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
+
+
+def test_null_handle_calls_are_rejected_not_fatal(nb):
+    """Every entry point validates its handle before touching CUDA: callable without a GPU."""
+    lib = nb.load_library()
+    null = C.c_void_p(None)
+    f, d, i = C.c_float(), C.c_double(), C.c_int()
+    sz = C.c_size_t()
+    assert lib.nbody_cuda_configure(null, 10, 0, 1) == -1
+    assert lib.nbody_cuda_slice(null, C.byref(sz), None, None, None) == -1
+    assert lib.nbody_cuda_upload_aos(null, None, 0) == -1
+    assert lib.nbody_cuda_download_aos(null, None, 0) == -1
+    assert lib.nbody_cuda_download_positions(null, None, 0) == -1
+    assert lib.nbody_cuda_step(null, 1.0, 0.5, 1.0, 1) == -1
+    assert lib.nbody_cuda_step_local(null, 1.0, 0.5, 1.0) == -1
+    assert lib.nbody_cuda_compute_step_aos(null, None, 0, 1.0, 0.5, 1.0) == -1
+    assert lib.nbody_cuda_synchronize(null) == -1
+    assert lib.nbody_cuda_last_step_ms(null, C.byref(f)) == -1
+    assert lib.nbody_cuda_profile_force(null, 1) == -1
+    assert lib.nbody_cuda_force_time(null, C.byref(d), C.byref(i), 0) == -1
+    assert lib.nbody_cuda_plan(null, None, None, None, None) == -1
+    assert lib.nbody_cuda_energy(null, 1.0, 1.0, C.byref(d), C.byref(d)) == -1
+    assert lib.nbody_cuda_generate(null, 0, 100.0, -1.0, 1.0, 1, C.byref(f)) == -1
+    assert lib.nbody_cuda_render_frame(null, 8, 8, 800.0, 0.0, 0.0, None) == -1
+    assert lib.nbody_cuda_peer_export(null, None) == -1
+    assert lib.nbody_cuda_peer_attach(null, 0, None) == -1
+    assert lib.nbody_cuda_peer_attach_local(null, 0, null) == -1
+    assert lib.nbody_cuda_exchange(null) == -1
+    assert lib.nbody_cuda_measure_fma_peak(null, 1, C.byref(d)) == -1
+    assert lib.nbody_cuda_launch_count(null) == 0
+    assert lib.nbody_cuda_stream(null) is None and lib.nbody_cuda_positions(null) is None
+    lib.nbody_cuda_destroy(null)                                     # a no-op
+    # the allocation-free entry point checks its size limit before anything else
+    err = C.create_string_buffer(200)
+    assert lib.nbody_cuda_accel_noalloc(None, None, 65537, 1.0, 1.0, None, err, len(err)) == -1
+    assert b"NBODY_NOALLOC_MAX_N" in err.value
+    assert lib.nbody_cuda_accel_noalloc(None, None, 0, 1.0, 1.0, None, err, len(err)) == 0
