@@ -84,18 +84,20 @@ __global__ void __launch_bounds__(THREADS, MINB) k_force(const float4* __restric
     }
 }
 
+static int g_dyn = 0;
 template <int I, int UNROLL, int THREADS, int MINB, int MODE>
 void run(const char* name, const float4* pos, float4* out, int n, int sm) {
     auto kern = k_force<I,UNROLL,THREADS,MINB,MODE>;
-    int occ=0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, 0);
+    if (g_dyn) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, g_dyn);
+    int occ=0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, g_dyn);
     cudaFuncAttributes fa; cudaFuncGetAttributes(&fa, kern);
     // choose number of i-tiles = exactly sm*occ*w so that there is no wave quantisation: wrap indices mod n
     int grid = sm * occ * 2;
     cudaEvent_t e0,e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-    kern<<<grid,THREADS>>>(pos,out,n,0.01f);
+    kern<<<grid,THREADS,g_dyn>>>(pos,out,n,0.01f);
     cudaDeviceSynchronize();
     float best=1e30f;
-    for (int r=0;r<3;r++){ cudaEventRecord(e0); kern<<<grid,THREADS>>>(pos,out,n,0.01f); cudaEventRecord(e1); cudaEventSynchronize(e1);
+    for (int r=0;r<3;r++){ cudaEventRecord(e0); kern<<<grid,THREADS,g_dyn>>>(pos,out,n,0.01f); cudaEventRecord(e1); cudaEventSynchronize(e1);
         float ms; cudaEventElapsedTime(&ms,e0,e1); if (ms<best) best=ms; }
     double inter = (double)grid*THREADS*I*(double)n;
     printf("%-28s I=%d U=%d T=%d minb=%d regs=%d occ=%d grid=%d  %.3f ms  %.3e int/s  %.1f TF20\n", name, I,UNROLL,THREADS,MINB, fa.numRegs, occ, grid, best, inter/(best*1e-3), inter/(best*1e-3)*20/1e12);
@@ -109,29 +111,16 @@ int main(int argc, char** argv){
     srand(1); for (auto& p: h){ p.x=rand()/(float)RAND_MAX*100; p.y=rand()/(float)RAND_MAX*100; p.z=rand()/(float)RAND_MAX*100; p.w=1.f; }
     float4 *pos,*out; cudaMalloc(&pos,n*sizeof(float4)); cudaMalloc(&out,n*sizeof(float4));
     cudaMemcpy(pos,h.data(),n*sizeof(float4),cudaMemcpyHostToDevice);
-    run<5,1,256,1,0>("packed", pos,out,n,sm);
-    run<5,2,256,1,0>("packed", pos,out,n,sm);
-    run<5,4,256,1,0>("packed", pos,out,n,sm);
-    run<6,1,256,1,0>("packed", pos,out,n,sm);
-    run<6,2,256,1,0>("packed", pos,out,n,sm);
-    run<6,4,256,1,0>("packed", pos,out,n,sm);
-    run<7,1,256,1,0>("packed", pos,out,n,sm);
-    run<7,2,256,1,0>("packed", pos,out,n,sm);
-    run<7,4,256,1,0>("packed", pos,out,n,sm);
-    run<8,1,256,1,0>("packed", pos,out,n,sm);
-    run<8,2,256,1,0>("packed", pos,out,n,sm);
-    run<8,4,256,1,0>("packed", pos,out,n,sm);
-    run<5,1,256,1,2>("unit", pos,out,n,sm);
-    run<5,2,256,1,2>("unit", pos,out,n,sm);
-    run<5,4,256,1,2>("unit", pos,out,n,sm);
-    run<6,1,256,1,2>("unit", pos,out,n,sm);
-    run<6,2,256,1,2>("unit", pos,out,n,sm);
-    run<6,4,256,1,2>("unit", pos,out,n,sm);
-    run<7,1,256,1,2>("unit", pos,out,n,sm);
-    run<7,2,256,1,2>("unit", pos,out,n,sm);
-    run<7,4,256,1,2>("unit", pos,out,n,sm);
-    run<8,1,256,1,2>("unit", pos,out,n,sm);
-    run<8,2,256,1,2>("unit", pos,out,n,sm);
-    run<8,4,256,1,2>("unit", pos,out,n,sm);
+    g_dyn = 0;
+    run<7,2,256,1,2>("unit 2w/smsp", pos,out,n,sm);
+    g_dyn = 120*1024;
+    run<7,2,128,1,2>("unit 1w/smsp", pos,out,n,sm);
+    run<7,4,128,1,2>("unit 1w/smsp", pos,out,n,sm);
+    run<8,2,128,1,2>("unit 1w/smsp", pos,out,n,sm);
+    run<10,2,128,1,2>("unit 1w/smsp", pos,out,n,sm);
+    run<12,1,128,1,2>("unit 1w/smsp", pos,out,n,sm);
+    run<12,2,128,1,2>("unit 1w/smsp", pos,out,n,sm);
+    run<7,2,128,1,0>("general 1w/smsp", pos,out,n,sm);
+    g_dyn = 0;
     return 0;
 }
