@@ -98,8 +98,9 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
                                               const u64 (&xi)[I], const u64 (&yi)[I], const u64 (&zi)[I],
                                               u64 eps2, u64 (&ax)[I], u64 (&ay)[I], u64 (&az)[I],
                                               int tile_slot0, int self_slot0) {
-    // the rare self-containing tiles are not worth code or registers: no unrolling there
-#pragma unroll(kMaskSelf ? 1 : 2)
+    // the self-containing tiles are unrolled like the others: in a small launch the CTA that owns
+    // them would otherwise finish last (N = 65 536: +1.4 % measured)
+#pragma unroll 2
     for (int q = 0; q < kTileJ / 2; ++q) {
         const float4 a = sA[q];
         const float4 b = sB[q];
