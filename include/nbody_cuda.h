@@ -135,7 +135,9 @@ int nbody_cuda_synchronize(nbody_cuda_t h);
 int nbody_cuda_last_step_ms(nbody_cuda_t h, float *ms);
 
 /* Per-kernel timing of the force kernel: when enabled every force launch is bracketed by CUDA
- * events; _force_time returns the sum over launches since the last reset, and their number. */
+ * events; _force_time returns the sum over launches since the last reset, and their number.
+ * enable > 1 additionally creates that many event pairs up front (none is then created between
+ * timed launches). */
 int nbody_cuda_profile_force(nbody_cuda_t h, int enable);
 int nbody_cuda_force_time(nbody_cuda_t h, double *total_ms, int *launches, int reset);
 

@@ -771,6 +771,15 @@ int nbody_cuda_last_step_ms(nbody_cuda_t h, float *ms) {
 int nbody_cuda_profile_force(nbody_cuda_t h, int enable) {
     if (!h) return NBODY_E_INVALID;
     h->profile_force = enable != 0;
+    if (enable > 1) {                       // reserve event pairs now, so that none is created between timed launches
+        CU_TRY(h, cudaSetDevice(h->device));
+        while (h->force_events.size() < (size_t)enable) {
+            cudaEvent_t a, b;
+            CU_TRY(h, cudaEventCreate(&a));
+            CU_TRY(h, cudaEventCreate(&b));
+            h->force_events.emplace_back(a, b);
+        }
+    }
     return NBODY_OK;
 }
 

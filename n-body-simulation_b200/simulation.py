@@ -256,8 +256,9 @@ class CudaNaiveSimulation:
         self._ck(self._lib.nbody_cuda_last_step_ms(self._h, C.byref(ms)))
         return ms.value
 
-    def profile_force(self, enable: bool = True) -> None:
-        self._ck(self._lib.nbody_cuda_profile_force(self._h, int(enable)))
+    def profile_force(self, enable: bool = True, reserve: int = 0) -> None:
+        """Bracket every force launch with CUDA events; `reserve` pre-creates that many event pairs."""
+        self._ck(self._lib.nbody_cuda_profile_force(self._h, max(int(reserve), 1) if enable else 0))
 
     def force_time(self, reset: bool = True):
         """(total milliseconds, launches) of the force kernel since the last reset."""
