@@ -277,8 +277,9 @@ int launch_force(nbody_cuda_t h, float G, float min_r2) {
         for (int r = 0; r < kMaxWorld; ++r) a.counts[r] = h->counts[r];
         a.G = G; a.eps2 = min_r2;
         if (h->mode == NBODY_MODE_FP64) {
-            const int grid = (int)((h->n_local + 2 * kThreads - 1) / (2 * kThreads));
-            force_fp64_kernel<<<grid, kThreads, 0, h->stream>>>(a);
+            constexpr int kT = 2;                      // targets per thread
+            const int grid = (int)((h->n_local + kT * kThreads - 1) / (kT * kThreads));
+            force_fp64_kernel<kT><<<grid, kThreads, 0, h->stream>>>(a);
             CHECK_LAUNCH(h, "force_fp64_kernel");
         } else {
             const int grid = (int)((h->n_local + kThreads - 1) / kThreads);

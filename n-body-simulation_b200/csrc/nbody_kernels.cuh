@@ -301,16 +301,33 @@ __global__ void __launch_bounds__(kThreads) force_strict_kernel(const StrictArgs
 // reference keeps (include/Particle.hpp:53-59) is FP32.  Two targets per thread; source tiles are
 // converted to double once per CTA on their way into shared memory.
 // ---------------------------------------------------------------------------------------------
+// 1/sqrt(x) in double from an FP32 seed: MUFU.RSQ on the FP32 value of x (relative error 2^-22),
+// one Newton step y <- y (1.5 - 0.5 x y^2) in double (error -> 1.5 e^2 ~ 5e-14, far below the final
+// rounding to FP32).  x must be a positive normal FP32-range number, which r^2 + eps^2 of FP32
+// positions is; x = 0 (coincident particles, no softening) gives inf like the reference's 1/sqrt(0).
+__device__ __forceinline__ double rsqrt_f64_from_f32_seed(double x, double half_x) {
+    const double y = (double)rsqrt_approx(__double2float_rn(x));
+    const double t = fma(-half_x, y * y, 1.5);
+    return y * t;
+}
+
+template <int kTargets>
 __global__ void __launch_bounds__(kThreads) force_fp64_kernel(const StrictArgs a) {
     __shared__ double4 tile[kTileJ];
     const int tid = threadIdx.x;
-    const int l0 = blockIdx.x * (2 * kThreads) + tid, l1 = l0 + kThreads;
-    const bool live0 = l0 < a.n_local, live1 = l1 < a.n_local;
-    const int slot0 = a.i_slot_begin + (live0 ? l0 : 0), slot1 = a.i_slot_begin + (live1 ? l1 : 0);
-    const float4 p0 = a.pos[slot0], p1 = a.pos[slot1];
-    const double x0 = p0.x, y0 = p0.y, z0 = p0.z, x1 = p1.x, y1 = p1.y, z1 = p1.z;
+    int slot[kTargets];
+    bool live[kTargets];
+    double xi[kTargets], yi[kTargets], zi[kTargets], ax[kTargets], ay[kTargets], az[kTargets];
+#pragma unroll
+    for (int k = 0; k < kTargets; ++k) {
+        const int l = blockIdx.x * (kTargets * kThreads) + k * kThreads + tid;
+        live[k] = l < a.n_local;
+        slot[k] = a.i_slot_begin + (live[k] ? l : 0);
+        const float4 p = a.pos[slot[k]];
+        xi[k] = p.x; yi[k] = p.y; zi[k] = p.z;
+        ax[k] = ay[k] = az[k] = 0.0;
+    }
     const double eps2 = (double)a.eps2;
-    double ax0 = 0, ay0 = 0, az0 = 0, ax1 = 0, ay1 = 0, az1 = 0;
     const int n_slots = a.world * a.slot_stride;
     for (int j0 = 0; j0 < n_slots; j0 += kTileJ) {
         __syncthreads();
@@ -319,30 +336,26 @@ __global__ void __launch_bounds__(kThreads) force_fp64_kernel(const StrictArgs a
             tile[tid] = make_double4((double)q.x, (double)q.y, (double)q.z, (double)q.w);
         }
         __syncthreads();
-#pragma unroll 4
+#pragma unroll 2
         for (int jj = 0; jj < kTileJ; ++jj) {
             const double4 q = tile[jj];
-            {
-                const double dx = q.x - x0, dy = q.y - y0, dz = q.z - z0;
+#pragma unroll
+            for (int k = 0; k < kTargets; ++k) {
+                const double dx = q.x - xi[k], dy = q.y - yi[k], dz = q.z - zi[k];
                 const double r2 = fma(dx, dx, fma(dy, dy, fma(dz, dz, eps2)));
-                const double ri = rsqrt(r2);
-                double s = q.w * ri * ri * ri;
-                s = (j0 + jj == slot0) ? 0.0 : s;
-                ax0 = fma(dx, s, ax0); ay0 = fma(dy, s, ay0); az0 = fma(dz, s, az0);
-            }
-            {
-                const double dx = q.x - x1, dy = q.y - y1, dz = q.z - z1;
-                const double r2 = fma(dx, dx, fma(dy, dy, fma(dz, dz, eps2)));
-                const double ri = rsqrt(r2);
-                double s = q.w * ri * ri * ri;
-                s = (j0 + jj == slot1) ? 0.0 : s;
-                ax1 = fma(dx, s, ax1); ay1 = fma(dy, s, ay1); az1 = fma(dz, s, az1);
+                const double ri = rsqrt_f64_from_f32_seed(r2, 0.5 * r2);
+                double s = (q.w * ri) * (ri * ri);
+                s = (j0 + jj == slot[k]) ? 0.0 : s;     // the reference skips j == i by index
+                ax[k] = fma(dx, s, ax[k]); ay[k] = fma(dy, s, ay[k]); az[k] = fma(dz, s, az[k]);
             }
         }
     }
     const double G = (double)a.G;
-    if (live0) a.acc[l0] = make_float4((float)(G * ax0), (float)(G * ay0), (float)(G * az0), 0.0f);
-    if (live1) a.acc[l1] = make_float4((float)(G * ax1), (float)(G * ay1), (float)(G * az1), 0.0f);
+#pragma unroll
+    for (int k = 0; k < kTargets; ++k) {
+        const int l = blockIdx.x * (kTargets * kThreads) + k * kThreads + tid;
+        if (live[k]) a.acc[l] = make_float4((float)(G * ax[k]), (float)(G * ay[k]), (float)(G * az[k]), 0.0f);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
