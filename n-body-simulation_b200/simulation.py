@@ -203,11 +203,15 @@ class CudaNaiveSimulation:
         p = _as_particles(particles)
         self._ck(self._lib.nbody_cuda_download_aos(self._h, p.ctypes.data_as(C.c_void_p), p.shape[0]))
 
-    def download_positions(self) -> np.ndarray:
+    def download_positions(self, out: np.ndarray | None = None) -> np.ndarray:
         """(count, 3) float32 positions of the local slice: one record of the reference's trajectory
-        file (src/CheckpointManager.cpp:86-99) without the 40-byte AoS detour."""
+        file (src/CheckpointManager.cpp:86-99) without the 40-byte AoS detour.  Pass a reusable
+        (ideally page-locked) `out` to avoid a fresh pageable allocation per record."""
         n = self.slice()["count"]
-        out = np.empty((n, 3), np.float32)
+        if out is None:
+            out = np.empty((n, 3), np.float32)
+        elif out.shape != (n, 3) or out.dtype != np.float32 or not out.flags["C_CONTIGUOUS"]:
+            raise ValueError(f"out must be a contiguous float32 array of shape ({n}, 3)")
         self._ck(self._lib.nbody_cuda_download_positions(self._h, out.ctypes.data_as(C.c_void_p), n))
         return out
 
