@@ -351,7 +351,7 @@ def run_ours(args):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64" if args.mode == "fp64" else "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {mirrors}", "n": n, "generator": gen, "G": 1.0, "dt": 0.5,
-                       "min_r2": eps, "mode": args.mode, "exchange": args.exchange if world > 1 else "none",
+                       "min_r2": eps, "mode": args.mode, "exchange": sim.exchange if world > 1 else "none",
                        "parallelism": f"i-slice x{world}", "l2": "flushed between steps (160 MiB memset, inside the timed region)",
                        "extra_warmup_steps": extra_warmup,
                        "plan": plan},

@@ -142,17 +142,32 @@ class CudaNaiveSimulation:
         return dict(begin=b.value, count=c.value, slot_begin=sb.value, slot_stride=ss.value)
 
     def _attach_peers(self) -> None:
+        """Swap the peer tokens and map every other rank's position block (CUDA IPC over NVLink).
+        If ANY rank cannot (no peer access between the devices, IPC not permitted in this
+        container), all ranks agree to use the NCCL all-gather exchange instead and say so."""
         tok = (C.c_ubyte * _lib.PEER_HANDLE_BYTES)()
         self._ck(self._lib.nbody_cuda_peer_export(self._h, tok))
         mine = bytes(tok)
         gathered = [None] * self.world
         self._dist.all_gather_object(gathered, mine, group=self.group)
+        ok, why = 1, ""
         for r, t in enumerate(gathered):
             if r == self.rank:
                 continue
             buf = (C.c_ubyte * _lib.PEER_HANDLE_BYTES).from_buffer_copy(t)
-            self._ck(self._lib.nbody_cuda_peer_attach(self._h, r, buf))
-        self._dist.barrier(group=self.group)
+            try:
+                self._ck(self._lib.nbody_cuda_peer_attach(self._h, r, buf))
+            except NBodyCudaError as e:
+                ok, why = 0, str(e)
+                break
+        flag = self._torch.tensor([ok], dtype=self._torch.int32, device=f"cuda:{self.device}")
+        self._dist.all_reduce(flag, op=self._dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 0:
+            import warnings
+
+            warnings.warn("peer-to-peer exchange unavailable" + (f" ({why})" if why else " on another rank") +
+                          "; using the NCCL all-gather exchange")
+            self.exchange = "nccl"      # mappings that did succeed stay unused until the next configure
 
     def _allgather_positions(self) -> None:
         """NCCL baseline: in-place all-gather of the current position array on the handle's stream."""
