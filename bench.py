@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--mode", default="fast", choices=["fast", "strict", "fp64"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-general", action="store_true", help="skip the general-loop (disk input) roofline measurement")
     ap.add_argument("--ref-n", type=int, default=0, help="sample size of the reference arm (default: chosen to bound its run time)")
     return ap.parse_args()
 
@@ -59,6 +60,17 @@ def workload_config(args):
     if args.particles:
         n = args.particles
     return n, gen, mirrors
+
+
+GENERATOR_SOURCE = ("nbody_b200.datasets (NumPy restatement of the reference's generatePlummerSphere / generateGalaxyDisk, "
+                    "src/Simulation.cpp:88-136,173-267: same distributions and softening rule, not the same mt19937 stream)")
+
+
+def shared_config(args, n, gen, mirrors, eps):
+    """The workload description -- the SAME dictionary in both arms, so the two lines compare like for like."""
+    return {"workload": f"{args.workload}: {mirrors}", "n": n, "generator": gen, "generator_source": GENERATOR_SOURCE,
+            "G": 1.0, "dt": 0.5, "min_r2": eps,
+            "l2": "GPU arm: flushed between steps (160 MiB memset, inside the timed region); CPU arm: not applicable"}
 
 
 def make_particles(nb, n, gen, seed=12345):
@@ -151,6 +163,11 @@ def cpu_reference_rate(p, eps, steps, threads, kind_hint=None):
     return float(n) * n * steps / secs, secs, kind
 
 
+def reference_sample_size(args, n, cores):
+    # bounded sample: ~1.5 s of wall time per step on `cores` threads at ~7 ns per interaction per core
+    return args.ref_n or int(min(n, max(4096, (1.5 * cores / 7e-9) ** 0.5 // 1024 * 1024)))
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -159,25 +176,33 @@ def run_reference(args):
 
     n, gen, mirrors = workload_config(args)
     cores = os.cpu_count() or 1
-    # bounded sample: ~1.5 s of wall time per step on `cores` threads at ~7 ns per interaction per core
-    n_s = args.ref_n or int(min(n, max(4096, (1.5 * cores / 7e-9) ** 0.5 // 1024 * 1024)))
+    n_s = reference_sample_size(args, n, cores)
     p, eps = make_particles(nb, n, gen)
     ps = p[:n_s].copy()
     if args.warmup:
         cpu_reference_rate(ps, eps, 1, cores)
-    t0 = time.perf_counter()
     rate, secs, kind = cpu_reference_rate(ps, eps, args.steps, cores)
     sample = (f"first {n_s} of {n} particles, {args.steps} steps, MpiNaiveSimulation on {cores} thread-ranks "
-              f"(oracle/mpi_shim), compute-only time" if kind == "reference"
+              f"(oracle/mpi_shim), compute-only time; rate is size-independent (N^2 law)" if kind == "reference"
               else f"first {n_s} of {n} particles, {args.steps} steps, row-order port on {cores} OpenMP threads")
+    # the reference's OWN clock (src/apps/headless_main.cpp:344-421): sim.step() + per-step gather to rank 0
+    own = None
+    if kind == "reference":
+        from oracle import Reference
+
+        _, secs_own = Reference().mpi_headless_loop(ps, 1.0, 0.5, eps, args.steps, nranks=cores)
+        own = {"value": float(n_s) * n_s * args.steps / secs_own, "unit": UNIT, "ms_per_step": secs_own / args.steps * 1e3,
+               "definition": "wall clock of the headless step loop as the reference measures it: NBodySimulation::step "
+                             "(computeStep + render-buffer copy) + per-step MPI_Gatherv of all particles to rank 0 "
+                             "(src/apps/headless_main.cpp:344-421, --disable-output); same sample"}
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {mirrors}", "n": n, "generator": gen, "G": 1.0, "dt": 0.5,
-                   "min_r2": eps, "note": "rate is size-independent (N^2 law); measured on a bounded sample"},
+        "config": shared_config(args, n, gen, mirrors, eps),
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "reference_own_clock": own,
         "gpu_launches": 0,
     }
     print(json.dumps(line))
@@ -187,6 +212,81 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
+def rel_err_rows(a, b):
+    import numpy as np
+
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    d = np.linalg.norm(b, axis=1)
+    return np.linalg.norm(a - b, axis=1) / np.where(d == 0, 1.0, d)
+
+
+def sharded_parity_check(nb, dist, local_rank, group, exchange, n=65536, steps=2):
+    """Before anything is timed at N > 1: the sharded path (i-slices by the reference's rule,
+    src/apps/headless_main.cpp:249-259, positions republished by the selected exchange) against the
+    UNSHARDED run of the same system on this rank's own device.  Strict mode must agree bit for bit in
+    every field (it reproduces the sequential NaiveSimulation whatever the rank count); fast mode within
+    rounding.  Unequal masses, so the general loop and the mass flag are exercised.  Returns the verdict
+    of all ranks (MIN / MAX reduced)."""
+    import numpy as np
+    import torch
+
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    p, eps = nb.datasets.plummer_sphere(n, 100.0, float(n), seed=777)
+    p["mass"] = np.random.default_rng(11).uniform(0.5, 2.0, n).astype(np.float32)
+    params = nb.SimParams(G=1.0, dt=0.5, min_r2=eps)
+    counts, displs = nb.slice_counts(n, world)
+    lo, cnt = displs[rank], counts[rank]
+    out = {"n": n, "steps": steps, "exchange": exchange}
+    strict_ok, fast_pos, fast_acc = 1, 0.0, 0.0
+    for mode in ("strict", "fast"):
+        single = nb.CudaNaiveSimulation(device=local_rank, mode=mode)
+        want = p.copy()
+        single.upload(want); single.step(params, steps); single.download(want)
+        single.close()
+        sim = nb.CudaNaiveSimulation(device=local_rank, mode=mode, group=group, exchange=exchange)
+        got = p[lo:lo + cnt].copy()
+        sim.upload(got, n_total=n); sim.step(params, steps); sim.download(got)
+        out["exchange"] = sim.exchange                    # "nccl" if peer mapping was refused on some rank
+        sim.close()
+        ref = want[lo:lo + cnt]
+        if mode == "strict":
+            strict_ok = int(got.tobytes() == ref.tobytes())
+        else:
+            fast_pos = float(rel_err_rows(got["position"], ref["position"]).max())
+            fast_acc = float(rel_err_rows(got["acceleration"], ref["acceleration"]).max())
+    t = torch.tensor([float(strict_ok), -fast_pos, -fast_acc], dtype=torch.float64, device=f"cuda:{local_rank}")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    out.update(strict_bitwise_vs_1gpu=bool(t[0].item() == 1.0), fast_max_rel_pos_vs_1gpu=float(-t[1].item()),
+               fast_max_rel_acc_vs_1gpu=float(-t[2].item()))
+    out["ok"] = out["strict_bitwise_vs_1gpu"] and out["fast_max_rel_pos_vs_1gpu"] < 1e-5 and out["fast_max_rel_acc_vs_1gpu"] < 1e-4
+    return out
+
+
+def general_loop_roofline(nb, sim, n, lo, cnt, nominal_peak, steps=3):
+    """The force kernel's general (unequal-mass) loop on the same N: the galaxy disk the reference's
+    sequential --random run uses (src/apps/headless_main.cpp:200-205; masses U[0.5,2) and one 1e6 body,
+    src/Simulation.cpp:92-98,121).  Same per-launch CUDA-event method as the headline roofline; outside
+    the headline's timed region."""
+    p, eps = make_particles(nb, n, "disk")
+    params = nb.SimParams(G=1.0, dt=0.5, min_r2=eps)
+    sim.upload(p[lo:lo + cnt].copy(), n_total=n)
+    sim.step(params, 1)                       # warm-up; the synchronising call below also teaches the host the mass flag
+    sim.synchronize()
+    sim.profile_force(True, reserve=steps + 1)
+    sim.force_time(reset=True)
+    for _ in range(steps):
+        sim.step(params, 1)
+    ms, launches = sim.force_time(reset=True)
+    sim.profile_force(False)
+    if not launches:
+        return None
+    flop = FLOP_PER_INTERACTION * float(cnt) * float(n)
+    achieved = flop / (ms / launches * 1e-3) / 1e12
+    return {"bound": "fp32_fma", "kernel": "force_fast_kernel (general loop: m_j multiplied in)", "input": "galaxy disk, unequal masses",
+            "achieved": achieved, "peak": nominal_peak, "unit": "TFLOP/s", "frac": achieved / nominal_peak,
+            "avg_launch_ms": ms / launches, "launches_timed": launches, "issue_ceiling_frac": 20.0 / 24.0}
+
+
 def run_ours(args):
     import torch
 
@@ -212,6 +312,16 @@ def run_ours(args):
     params = nb.SimParams(G=1.0, dt=0.5, min_r2=eps)   # headless_main.cpp:33-36 + generator's softening
     counts, displs = nb.slice_counts(n, world)
     lo, cnt = displs[rank], counts[rank]
+
+    parity = None
+    if world > 1:
+        parity = sharded_parity_check(nb, dist, local_rank, group, args.exchange)
+        if not parity["ok"]:
+            if rank == 0:
+                print(json.dumps({"error": "sharded run disagrees with the single-GPU run", "parity": parity}))
+            dist.barrier()
+            dist.destroy_process_group()
+            return 3
 
     sim = nb.CudaNaiveSimulation(device=local_rank, mode=args.mode, group=group, exchange=args.exchange)
     lib = nb.load_library()
@@ -334,9 +444,14 @@ def run_ours(args):
         "issue_ceiling_frac": 20.0 / 24.0,
     }
 
-    # ---- CPU baseline: the reference's sequential path on a bounded sample (rank 0, N = 1 only) ----
+    # ---- the general (unequal-mass) loop of the same kernel, same N, disk input ----
+    roofline_general = None
+    if args.mode == "fast" and not args.no_general:
+        roofline_general = general_loop_roofline(nb, sim, n, lo, cnt, nominal_peak)
+
+    # ---- CPU baseline: the reference's sequential path on a bounded sample (rank 0) ----
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and not args.no_cpu_baseline:
         n_s = min(n, 32768)                                 # ~5e8 pair evaluations per step: 5-10 s on one core
         ps = p[:n_s].copy()
         rate, secs, kind = cpu_reference_rate(ps, eps, 2, 1)
@@ -350,12 +465,12 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64" if args.mode == "fp64" else "f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {mirrors}", "n": n, "generator": gen, "G": 1.0, "dt": 0.5,
-                       "min_r2": eps, "mode": args.mode, "exchange": sim.exchange if world > 1 else "none",
-                       "parallelism": f"i-slice x{world}", "l2": "flushed between steps (160 MiB memset, inside the timed region)",
-                       "extra_warmup_steps": extra_warmup,
-                       "plan": plan},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches), "roofline": roofline, "cpu_baseline": cpu,
+            "config": shared_config(args, n, gen, mirrors, eps),
+            "details": {"mode": args.mode, "exchange": sim.exchange if world > 1 else "none",
+                        "parallelism": f"i-slice x{world}", "extra_warmup_steps": extra_warmup, "plan": plan},
+            "parity": parity if world > 1 else "single GPU: checked against the oracle by tests/ and smoke()",
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches), "roofline": roofline,
+            "roofline_general": roofline_general, "cpu_baseline": cpu,
         }
         print(json.dumps(line))
     sim.close()

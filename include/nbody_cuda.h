@@ -40,7 +40,8 @@ typedef struct nbody_cuda *nbody_cuda_t;
 
 /* arithmetic modes */
 #define NBODY_MODE_FAST 0   /* FP32, packed FFMA2 + MUFU.RSQ, blocked summation (the product)            */
-#define NBODY_MODE_STRICT 1 /* FP32, the reference's exact operation order and rounding: bit-identical */
+#define NBODY_MODE_STRICT 1 /* FP32, the exact operation order and rounding of the SEQUENTIAL NaiveSimulation: bit-identical to it
+                               for any world size; not to MpiNaiveSimulation, whose summation order depends on the rank count */
 #define NBODY_MODE_FP64 2   /* forces summed in FP64 from the FP32 state, rounded to FP32 once; optional, no counterpart */
 
 /* Size of the record this library reads and writes; equals sizeof(particle_t) = 40
@@ -142,9 +143,32 @@ int nbody_cuda_profile_force(nbody_cuda_t h, int enable);
 int nbody_cuda_force_time(nbody_cuda_t h, double *total_ms, int *launches, int reset);
 
 /* Work plan of the fast force kernel for the current configuration (no counterpart in the
- * reference): targets held per thread, persistent grid size, and the target-tile x source-tile
- * rectangle that is cut evenly across that grid.  Any pointer may be NULL. */
+ * reference): targets held per thread in the main target tiles, persistent grid size, number of
+ * target tiles (main tiles plus up to two narrower tail tiles) and of 256-source tiles; the
+ * tiles x sources rectangle is cut across the grid in 32-source granules of equal cost.  Any
+ * pointer may be NULL. */
 int nbody_cuda_plan(nbody_cuda_t h, int *targets_per_thread, int *grid, int *target_tiles, int *source_tiles);
+
+/* The same plan as pure host arithmetic, for any slice shape and SM count -- needs no device, so
+ * the plan's invariants (every granule owned by exactly one CTA, no empty CTA, the owner formula
+ * the finishing kernel uses) are testable on a CPU-only machine.  n_slots is the padded source
+ * count (multiple of 256), targets_per_thread 0 lets the plan choose.
+ *   header[12]       I_main, n_main, n_tail, tail_I[0], tail_I[1], grid, granules per tile, total cost,
+ *                    CTAs per SM, scratch float4s, sources per granule, tiles
+ *   first_gran       [grid + 1] first global granule of each CTA (and the end), or NULL
+ *   tile_owner_*     [tiles] first and last CTA that contribute to each target tile, or NULL */
+int nbody_cuda_plan_describe(size_t n_local, size_t n_slots, int sm_count, int targets_per_thread, long long *header,
+                             long long *first_gran, size_t first_gran_len, int *tile_owner_first, int *tile_owner_last,
+                             size_t tiles_len);
+
+/* Tuning and diagnostic switches of a handle (no counterpart in the reference).
+ *   NBODY_OPT_TARGETS_PER_THREAD  0 (default): the plan chooses; 1, 2, 4 or 7 forces the main tile width.
+ *   NBODY_OPT_BARRIER_TIMEOUT_MS  how long the device-side wait for a peer's step counter may last before
+ *                                 the run is reported as faulted (default 30 000); raise it for steps that
+ *                                 take longer than that (strict / FP64 modes at very large N). */
+#define NBODY_OPT_TARGETS_PER_THREAD 2
+#define NBODY_OPT_BARRIER_TIMEOUT_MS 3
+int nbody_cuda_set_option(nbody_cuda_t h, int option, long long value);
 
 /* Number of kernels this library has launched on the handle since creation. */
 long long nbody_cuda_launch_count(nbody_cuda_t h);
@@ -173,6 +197,15 @@ int nbody_cuda_peer_export(nbody_cuda_t h, void *token_out);
 int nbody_cuda_peer_attach(nbody_cuda_t h, int peer_rank, const void *token);
 /* Same-process variant (one process driving several GPUs): attach another handle directly. */
 int nbody_cuda_peer_attach_local(nbody_cuda_t h, int peer_rank, nbody_cuda_t peer);
+/* Waits for this handle's stream and unmaps every attached peer block.  TEAR-DOWN ORDER for peers in
+ * other processes: CUDA requires that an exported block is not freed while another process still
+ * has it open, so before any rank destroys or reconfigures its handle (both free the block),
+ *   1. every rank calls nbody_cuda_peer_detach_all,
+ *   2. the ranks meet at a host barrier (MPI_Barrier / torch.distributed.barrier),
+ *   3. only then nbody_cuda_destroy / nbody_cuda_configure.
+ * (The reference's ranks have nothing to unmap: MPI_Sendrecv owns its buffers,
+ * src/MpiNaiveSimulation.cpp:106-120.) */
+int nbody_cuda_peer_detach_all(nbody_cuda_t h);
 
 /* Publishes the local slice of the CURRENT position array to every attached peer and waits for
  * theirs (the exchange that must follow nbody_cuda_upload_aos when world > 1). */
@@ -203,7 +236,11 @@ int nbody_cuda_measure_fma_peak(nbody_cuda_t h, int packed, double *flops_per_se
  * lives on that GPU (cudaGetSymbolAddress); make that first call before any stream capture begins.
  * All calls share the one array and it keeps whatever the previous call left (each call rewrites
  * everything it reads, so nothing needs clearing): calls whose kernels overlap on the same GPU
- * -- two streams, two threads -- race; serialise them. */
+ * -- two streams, two threads -- race; serialise them.  d_accelerations may be the same buffer as
+ * d_positions (the sources are copied into the built-in array before anything is written).  The
+ * per-device look-up is remembered for the life of the process and is safe to trigger from several
+ * host threads at once; it does not survive cudaDeviceReset -- after a reset, do not call this entry
+ * point again in the same process. */
 #define NBODY_NOALLOC_MAX_N 65536
 int nbody_cuda_accel_noalloc(const void *d_positions, void *d_accelerations, size_t n, float G, float min_r2,
                              void *stream, char *err, size_t err_len);

@@ -19,6 +19,8 @@ MODE_FAST = 0
 MODE_STRICT = 1
 MODE_FP64 = 2
 PEER_HANDLE_BYTES = 128
+OPT_TARGETS_PER_THREAD = 2
+OPT_BARRIER_TIMEOUT_MS = 3
 
 
 class NBodyCudaError(RuntimeError):
@@ -63,6 +65,9 @@ SIGNATURES = {
     "nbody_cuda_profile_force": (_i, [_vp, _i]),
     "nbody_cuda_force_time": (_i, [_vp, C.POINTER(_d), C.POINTER(_i), _i]),
     "nbody_cuda_plan": (_i, [_vp, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)]),
+    "nbody_cuda_plan_describe": (_i, [_sz, _sz, _i, _i, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), _sz,
+                                      C.POINTER(_i), C.POINTER(_i), _sz]),
+    "nbody_cuda_set_option": (_i, [_vp, _i, C.c_longlong]),
     "nbody_cuda_launch_count": (C.c_longlong, [_vp]),
     "nbody_cuda_energy": (_i, [_vp, _f, _f, C.POINTER(_d), C.POINTER(_d)]),
     "nbody_cuda_stream": (_vp, [_vp]),
@@ -70,6 +75,7 @@ SIGNATURES = {
     "nbody_cuda_peer_export": (_i, [_vp, _vp]),
     "nbody_cuda_peer_attach": (_i, [_vp, _i, _vp]),
     "nbody_cuda_peer_attach_local": (_i, [_vp, _i, _vp]),
+    "nbody_cuda_peer_detach_all": (_i, [_vp]),
     "nbody_cuda_exchange": (_i, [_vp]),
     "nbody_cuda_measure_fma_peak": (_i, [_vp, _i, C.POINTER(_d)]),
     "nbody_cuda_accel_noalloc": (_i, [_vp, _vp, _sz, _f, _f, _vp, C.c_char_p, _sz]),

@@ -10,6 +10,7 @@
 #include <string.h>
 #include <unistd.h>
 
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -60,6 +61,10 @@ struct nbody_cuda {
     int mass_state = -1;         // host copy of the flag: -1 not read yet, 0 unequal masses, 1 all equal
     unsigned barrier_seq = 0;
     unsigned long long barrier_timeout_ns = 30ull * 1000000000ull;
+    // barrier fault word in page-locked, device-mapped host memory: the waiting kernel writes it, the
+    // host reads it without touching the stream (so a faulted run is refused before more work is queued)
+    volatile unsigned *host_fault = nullptr;
+    unsigned *dev_fault = nullptr;
 
     // local state
     float4 *vel = nullptr, *acc = nullptr;
@@ -75,6 +80,7 @@ struct nbody_cuda {
     int targets_per_thread = 4;
     ForcePlan plan{};
     int force_occupancy = 2;
+    int forced_I = 0;                  // NBODY_OPT_TARGETS_PER_THREAD (0: chosen by the plan)
 
     // peers
     bool attached[kMaxWorld] = {false};
@@ -129,7 +135,7 @@ int fail(nbody_cuda_t h, int code, const std::string &msg) {
 size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // words of the 64-word flag block that follows the position arrays
-constexpr int kFaultWord = 32;    // flags[0..15]: barrier counters, flags[32]: barrier fault
+// flags[0..15]: barrier counters (the barrier fault word lives in host-mapped memory, see nbody_cuda::host_fault)
 constexpr int kMassInfoWord = 40; // flags[40]: masses differ, flags[41]: bits of the common mass
 constexpr int kDoneWord = 48;     // flags[48]: CTA ticket counter of the finishing kernel
 
@@ -170,43 +176,74 @@ void free_buffers(nbody_cuda_t h) {
     h->configured = false;
 }
 
-// Targets-per-thread variants of the fast kernel and their measured relative speed (B200,
-// tools/exp/force_variants.cu): more targets per thread = fewer shared-memory reads and better
-// operand reuse, until registers run out.
-struct Variant { int I; int ctas_per_sm; double speed; };
-const Variant kVariants[] = {{1, 2, 0.80}, {2, 2, 0.90}, {4, 1, 0.95}, {6, 1, 0.99}, {7, 1, 1.00}, {8, 1, 0.97}};
+// Targets-per-thread variants of the fast kernel (main tiles); narrower tail tiles come from
+// {4, 2, 1} below the main width.  More targets per thread = fewer shared-memory reads per
+// interaction and better operand reuse, until registers run out (I = 7: 200-odd registers).
+struct Variant { int I; int ctas_per_sm; };
+const Variant kVariants[] = {{7, 1}, {4, 1}, {2, 2}, {1, 2}};
+constexpr int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
 
 ForcePlan plan_for(size_t n_local, size_t n_slots, int sm_count, const Variant &v) {
-    const int TI = kThreads * v.I;
+    const size_t TI = (size_t)kThreads * v.I;
     ForcePlan p;
-    p.n_itiles = (int)((n_local + TI - 1) / TI);
-    p.n_jtiles = (int)(n_slots / kTileJ);
-    p.units = (long long)p.n_itiles * p.n_jtiles;
+    memset(&p, 0, sizeof(p));
+    p.I_main = v.I;
+    p.n_gran = (int)(n_slots / kGran);
+    p.n_main = (int)(n_local / TI);
+    int blocks = (int)((n_local - (size_t)p.n_main * TI + kThreads - 1) / kThreads);    // 256-target blocks left over
+    if (blocks >= v.I) { p.n_main++; blocks = 0; }
+    for (int w = 4; w >= 1 && p.n_tail < kMaxTail; w >>= 1)       // blocks < I <= 7: at most two of {4,2,1}
+        if (w < v.I && blocks >= w) { p.tail_I[p.n_tail++] = w; blocks -= w; }
+    if (blocks > 0) {                                            // not representable (cannot happen for I in {7,4,2,1})
+        p.n_main++; p.n_tail = 0; p.tail_I[0] = p.tail_I[1] = 0;
+    }
+    p.cost_main = plan_granule_cost(v.I);
+    int max_cost = p.n_main > 0 ? p.cost_main : 0;
+    p.cost_total = (long long)p.n_main * p.n_gran * p.cost_main;
+    for (int k = 0; k < p.n_tail; ++k) {
+        p.cost_tail[k] = plan_granule_cost(p.tail_I[k]);
+        p.cost_total += (long long)p.n_gran * p.cost_tail[k];
+        if (p.cost_tail[k] > max_cost) max_cost = p.cost_tail[k];
+    }
     long long g = (long long)sm_count * v.ctas_per_sm;
-    if (g > p.units) g = p.units;
+    if (max_cost > 0 && g > p.cost_total / max_cost) g = p.cost_total / max_cost;   // every CTA gets at least one granule
     if (g < 1) g = 1;
     p.grid = (int)g;
     return p;
 }
 
-// Chooses the variant with the smallest estimated time: the busiest SM's share of the
-// (padded) interaction rectangle divided by the variant's speed.
-int make_plan(nbody_cuda_t h) {
+// Estimated duration of a plan in granule-cost units: the busiest CTA's share (plus one granule of
+// imbalance) and what each of its segments costs besides the interactions -- target loads and the
+// first source tile at L2 latency (~2000 cycles), clearing and writing the partial sums.
+double plan_estimate(const ForcePlan &p, int sm_count) {
+    const double share = (double)p.cost_total / p.grid;
+    const int max_cost = p.n_main > 0 ? p.cost_main : p.cost_tail[0];
+    const double per_tile = (double)p.n_gran * max_cost;
+    const double segments = 1.0 + share / per_tile;
+    const int resident = (p.grid + sm_count - 1) / sm_count;     // CTAs sharing an SM split its FMA pipe
+    return (share + max_cost + segments * (26.0 + 2.0 * p.I_main)) * resident;
+}
+
+int pick_variant(size_t n_local, size_t n_slots, int sm_count, int forced_I, ForcePlan *plan) {
     double best = 0.0;
     int best_k = -1;
-    for (int k = 0; k < (int)(sizeof(kVariants) / sizeof(kVariants[0])); ++k) {
-        const Variant &v = kVariants[k];
-        const ForcePlan p = plan_for(h->n_local, h->n_slots, h->sm_count, v);
-        const long long per_cta = (p.units + p.grid - 1) / p.grid;                  // units of the busiest CTA
-        const int resident = (p.grid + h->sm_count - 1) / h->sm_count;              // CTAs sharing its SM
-        const double t = (double)per_cta * resident * v.I / v.speed;
+    for (int k = 0; k < kNumVariants; ++k) {
+        if (forced_I > 0 && kVariants[k].I != forced_I) continue;
+        const ForcePlan p = plan_for(n_local, n_slots, sm_count, kVariants[k]);
+        const double t = plan_estimate(p, sm_count);
         if (best_k < 0 || t < best) { best = t; best_k = k; }
     }
-    const Variant &v = kVariants[best_k];
-    h->targets_per_thread = v.I;
-    h->force_occupancy = v.ctas_per_sm;
-    h->plan = plan_for(h->n_local, h->n_slots, h->sm_count, v);
-    const size_t need = ((size_t)h->plan.grid + h->plan.n_itiles) * kThreads * v.I;
+    if (best_k < 0) return pick_variant(n_local, n_slots, sm_count, 0, plan);     // unknown forced width: choose freely
+    *plan = plan_for(n_local, n_slots, sm_count, kVariants[best_k]);
+    return best_k;
+}
+
+// Chooses the variant with the smallest estimated time and sizes the partial-sum scratch.
+int make_plan(nbody_cuda_t h) {
+    const int k = pick_variant(h->n_local, h->n_slots, h->sm_count, h->forced_I, &h->plan);
+    h->targets_per_thread = kVariants[k].I;
+    h->force_occupancy = kVariants[k].ctas_per_sm;
+    const size_t need = plan_partial_slots(h->plan);
     if (need > h->partial_cap) {
         if (h->partial) cudaFree(h->partial);
         h->partial = nullptr; h->partial_cap = 0;
@@ -225,15 +262,13 @@ int ensure_aos(nbody_cuda_t h, size_t bytes) {
     return NBODY_OK;
 }
 
-template <bool kUnit>
+template <int kLoop>
 void launch_fast_variant(int I, int grid, cudaStream_t st, const ForceArgs &a) {
     switch (I) {
-        case 8: force_fast_kernel<8, kUnit><<<grid, kThreads, 0, st>>>(a); break;
-        case 7: force_fast_kernel<7, kUnit><<<grid, kThreads, 0, st>>>(a); break;
-        case 6: force_fast_kernel<6, kUnit><<<grid, kThreads, 0, st>>>(a); break;
-        case 4: force_fast_kernel<4, kUnit><<<grid, kThreads, 0, st>>>(a); break;
-        case 2: force_fast_kernel<2, kUnit><<<grid, kThreads, 0, st>>>(a); break;
-        default: force_fast_kernel<1, kUnit><<<grid, kThreads, 0, st>>>(a); break;
+        case 7: force_fast_kernel<7, kLoop><<<grid, kThreads, 0, st>>>(a); break;
+        case 4: force_fast_kernel<4, kLoop><<<grid, kThreads, 0, st>>>(a); break;
+        case 2: force_fast_kernel<2, kLoop><<<grid, kThreads, 0, st>>>(a); break;
+        default: force_fast_kernel<1, kLoop><<<grid, kThreads, 0, st>>>(a); break;
     }
 }
 
@@ -291,15 +326,16 @@ int launch_force(nbody_cuda_t h, float G, float min_r2) {
         a.pos = h->pos[h->cur]; a.partial = h->partial;
         a.n_local = (int)h->n_local; a.i_slot_begin = (int)(h->rank * h->slot_stride);
         a.eps2 = min_r2; a.plan = h->plan;
+        a.mask_self = !(min_r2 >= kMaskSelfBelowEps2);          // also masks for NaN / negative softening
         a.mass_info = h->flags + kMassInfoWord;
         // until the host has seen the mass flag (first synchronising call after an upload) both loops
         // are enqueued and the one that does not apply exits immediately
         if (h->mass_state != 0) {
-            launch_fast_variant<true>(h->targets_per_thread, h->plan.grid, h->stream, a);
+            launch_fast_variant<kLoopUnit>(h->targets_per_thread, h->plan.grid, h->stream, a);
             CHECK_LAUNCH(h, "force_fast_kernel<uniform mass>");
         }
         if (h->mass_state != 1) {
-            launch_fast_variant<false>(h->targets_per_thread, h->plan.grid, h->stream, a);
+            launch_fast_variant<kLoopMassMul>(h->targets_per_thread, h->plan.grid, h->stream, a);
             CHECK_LAUNCH(h, "force_fast_kernel<general>");
         }
     }
@@ -328,16 +364,20 @@ void learn_mass_state(nbody_cuda_t h) {
         cudaGetLastError();
 }
 
-// Reports a barrier that gave up (a peer never arrived).  Called after a stream synchronise.
-int check_fault(nbody_cuda_t h) {
-    learn_mass_state(h);
-    if (h->world == 1 || !h->flags) return NBODY_OK;
-    unsigned f = 0;
-    CU_TRY(h, cudaMemcpy(&f, h->flags + kFaultWord, sizeof(f), cudaMemcpyDeviceToHost));
+// Reports a barrier that gave up (a peer never arrived).  Reads host memory only.
+int report_fault(nbody_cuda_t h) {
+    const unsigned f = h->host_fault ? *h->host_fault : 0u;
     if (f != 0)
         return fail(h, NBODY_E_CUDA, "peer exchange timed out waiting for rank " + std::to_string((int)f - 1) +
-                                         " (ranks out of step, or a peer process died)");
+                                         " (ranks out of step, or a peer process died); positions from that step on are "
+                                         "stale -- upload again (or reconfigure) to clear the fault");
     return NBODY_OK;
+}
+
+// Called after a stream synchronise.
+int check_fault(nbody_cuda_t h) {
+    learn_mass_state(h);
+    return report_fault(h);
 }
 
 unsigned *peer_flags_of(nbody_cuda_t h, int r) {
@@ -360,7 +400,7 @@ int launch_barrier(nbody_cuda_t h, bool already_signalled) {
     }
     WaitArgs w;
     w.seq = h->barrier_seq; w.my_rank = h->rank; w.world = h->world; w.flags = h->flags;
-    w.fault = h->flags + kFaultWord; w.timeout_ns = h->barrier_timeout_ns;
+    w.fault = h->dev_fault; w.timeout_ns = h->barrier_timeout_ns;
     wait_kernel<<<1, 32, 0, h->stream>>>(w);
     CHECK_LAUNCH(h, "wait_kernel");
     return NBODY_OK;
@@ -445,12 +485,16 @@ int nbody_cuda_create(nbody_cuda_t *out, int device, int mode) {
     if ((e = cudaSetDevice(device)) != cudaSuccess ||
         (e = cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaEventCreate(&h->ev_begin)) != cudaSuccess || (e = cudaEventCreate(&h->ev_end)) != cudaSuccess) {
+        (e = cudaEventCreate(&h->ev_begin)) != cudaSuccess || (e = cudaEventCreate(&h->ev_end)) != cudaSuccess ||
+        (e = cudaHostAlloc((void **)&h->host_fault, 64, cudaHostAllocMapped)) != cudaSuccess ||
+        (e = cudaHostGetDevicePointer((void **)&h->dev_fault, (void *)h->host_fault, 0)) != cudaSuccess) {
         std::string msg = std::string("nbody_cuda_create: ") + cudaGetErrorString(e);
         cudaGetLastError();
+        if (h->host_fault) cudaFreeHost((void *)h->host_fault);
         delete h;
         return fail(nullptr, NBODY_E_CUDA, msg);
     }
+    *h->host_fault = 0u;
     *out = h;
     return NBODY_OK;
 }
@@ -464,6 +508,7 @@ void nbody_cuda_destroy(nbody_cuda_t h) {
     if (h->ev_begin) cudaEventDestroy(h->ev_begin);
     if (h->ev_end) cudaEventDestroy(h->ev_end);
     if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->host_fault) cudaFreeHost((void *)h->host_fault);
     cudaGetLastError();
     delete h;
 }
@@ -474,7 +519,7 @@ int nbody_cuda_configure(nbody_cuda_t h, size_t n_total, int rank, int world) {
     if (!h) return NBODY_E_INVALID;
     if (world < 1 || world > kMaxWorld || rank < 0 || rank >= world)
         return fail(h, NBODY_E_INVALID, "nbody_cuda_configure: need 0 <= rank < world <= 16");
-    if (n_total > (size_t)1 << 30) return fail(h, NBODY_E_INVALID, "nbody_cuda_configure: n_total above 2^30");
+    if (n_total > ((size_t)1 << 30) - kSlotAlign) return fail(h, NBODY_E_INVALID, "nbody_cuda_configure: n_total above 2^30 - 256");
     CU_TRY(h, cudaSetDevice(h->device));
     if (h->configured && n_total == h->n_total && rank == h->rank && world == h->world) return NBODY_OK;
 
@@ -486,7 +531,8 @@ int nbody_cuda_configure(nbody_cuda_t h, size_t n_total, int rank, int world) {
     size_t max_count = n_total / world + (n_total % world ? 1 : 0);
     const size_t stride = round_up(max_count > 0 ? max_count : 1, kSlotAlign);
     const size_t n_slots = stride * world;
-    if (n_slots > (size_t)0x7fffff00) return fail(h, NBODY_E_INVALID, "nbody_cuda_configure: too many slots");
+    // 2 * n_slots (both position arrays) and every slot index must fit a 32-bit int
+    if (n_slots > ((size_t)1 << 30) - kSlotAlign) return fail(h, NBODY_E_INVALID, "nbody_cuda_configure: too many slots (limit 2^30 - 256 including padding)");
     const size_t block_bytes = 2 * n_slots * sizeof(float4) + 256;
 
     if (block_bytes > h->block_bytes || n_slots != h->n_slots) {
@@ -514,6 +560,7 @@ int nbody_cuda_configure(nbody_cuda_t h, size_t n_total, int rank, int world) {
     h->barrier_seq = 0;
     h->mass_checked = false;
     h->mass_state = -1;
+    *h->host_fault = 0u;        // the stream is idle: a new configuration starts unfaulted
     // everything is padding until particles arrive
     const int total = (int)(2 * n_slots);
     pad_kernel<<<(total + 255) / 256, 256, 0, h->stream>>>(h->pos[0], 0, total);
@@ -544,6 +591,10 @@ int nbody_cuda_upload_aos(nbody_cuda_t h, const void *particles, size_t count) {
     if (count != h->n_local) return fail(h, NBODY_E_INVALID, "nbody_cuda_upload_aos: count differs from the configured slice");
     if (count && !particles) return fail(h, NBODY_E_INVALID, "nbody_cuda_upload_aos: particles is NULL");
     CU_TRY(h, cudaSetDevice(h->device));
+    if (*h->host_fault != 0u) {                 // a barrier gave up earlier: new particles restart the run
+        CU_TRY(h, cudaStreamSynchronize(h->stream));
+        *h->host_fault = 0u;
+    }
     if (count == 0) return NBODY_OK;
     const size_t bytes = count * kRecFloats * sizeof(float);
     int rc = ensure_aos(h, bytes);
@@ -687,6 +738,7 @@ int nbody_cuda_step(nbody_cuda_t h, float G, float dt, float min_r2, int n_steps
     if (n_steps < 0) return fail(h, NBODY_E_INVALID, "nbody_cuda_step: n_steps < 0");
     if (h->world > 1 && !all_peers_attached(h))
         return fail(h, NBODY_E_STATE, "nbody_cuda_step: world > 1 needs every peer attached (or use nbody_cuda_step_local + an all-gather)");
+    if (report_fault(h) != NBODY_OK) return NBODY_E_CUDA;      // an earlier exchange timed out: do not step on stale positions
     CU_TRY(h, cudaSetDevice(h->device));
     int done = 0;
     const bool use_graph = h->world == 1 && !h->profile_force && n_steps >= 4 && h->n_local > 0;
@@ -806,9 +858,56 @@ int nbody_cuda_plan(nbody_cuda_t h, int *targets_per_thread, int *grid, int *tar
     if (!h->configured) return fail(h, NBODY_E_STATE, "nbody_cuda_plan: not configured");
     if (targets_per_thread) *targets_per_thread = h->targets_per_thread;
     if (grid) *grid = h->plan.grid;
-    if (target_tiles) *target_tiles = h->plan.n_itiles;
-    if (source_tiles) *source_tiles = h->plan.n_jtiles;
+    if (target_tiles) *target_tiles = plan_tiles(h->plan);
+    if (source_tiles) *source_tiles = h->plan.n_gran * kGran / kTileJ;
     return NBODY_OK;
+}
+
+int nbody_cuda_plan_describe(size_t n_local, size_t n_slots, int sm_count, int targets_per_thread, long long *header,
+                             long long *first_gran, size_t first_gran_len, int *tile_owner_first, int *tile_owner_last,
+                             size_t tiles_len) {
+    if (!header || n_local == 0 || n_slots == 0 || n_slots % kTileJ != 0 || sm_count < 1 || n_local > n_slots)
+        return NBODY_E_INVALID;
+    ForcePlan p;
+    const int k = pick_variant(n_local, n_slots, sm_count, targets_per_thread, &p);
+    header[0] = p.I_main; header[1] = p.n_main; header[2] = p.n_tail; header[3] = p.tail_I[0]; header[4] = p.tail_I[1];
+    header[5] = p.grid; header[6] = p.n_gran; header[7] = p.cost_total; header[8] = kVariants[k].ctas_per_sm;
+    header[9] = (long long)plan_partial_slots(p); header[10] = kGran; header[11] = plan_tiles(p);
+    if (first_gran) {
+        if (first_gran_len < (size_t)p.grid + 1) return NBODY_E_INVALID;
+        for (int c = 0; c <= p.grid; ++c) first_gran[c] = plan_first_gran(p, c);
+    }
+    if (tile_owner_first && tile_owner_last) {
+        if (tiles_len < (size_t)plan_tiles(p)) return NBODY_E_INVALID;
+        for (int t = 0; t < plan_tiles(p); ++t) {
+            tile_owner_first[t] = plan_owner(p, (long long)t * p.n_gran);
+            tile_owner_last[t] = plan_owner(p, (long long)(t + 1) * p.n_gran - 1);
+        }
+    }
+    return NBODY_OK;
+}
+
+int nbody_cuda_set_option(nbody_cuda_t h, int option, long long value) {
+    if (!h) return NBODY_E_INVALID;
+    switch (option) {
+        case NBODY_OPT_TARGETS_PER_THREAD:
+            if (value != 0 && value != 1 && value != 2 && value != 4 && value != 7)
+                return fail(h, NBODY_E_INVALID, "nbody_cuda_set_option: targets per thread must be 0 (automatic), 1, 2, 4 or 7");
+            h->forced_I = (int)value;
+            if (h->configured && h->mode == NBODY_MODE_FAST && h->n_local > 0) {
+                CU_TRY(h, cudaSetDevice(h->device));
+                CU_TRY(h, cudaStreamSynchronize(h->stream));
+                drop_graph(h);
+                return make_plan(h);
+            }
+            return NBODY_OK;
+        case NBODY_OPT_BARRIER_TIMEOUT_MS:
+            if (value < 1) return fail(h, NBODY_E_INVALID, "nbody_cuda_set_option: barrier time-out must be at least 1 ms");
+            h->barrier_timeout_ns = (unsigned long long)value * 1000000ull;
+            return NBODY_OK;
+        default:
+            return fail(h, NBODY_E_INVALID, "nbody_cuda_set_option: unknown option");
+    }
 }
 
 long long nbody_cuda_launch_count(nbody_cuda_t h) { return h ? h->launches : 0; }
@@ -901,6 +1000,14 @@ int nbody_cuda_peer_attach_local(nbody_cuda_t h, int peer_rank, nbody_cuda_t pee
     h->peer_is_ipc[peer_rank] = false;
     h->attached[peer_rank] = true;
     h->n_attached++;
+    return NBODY_OK;
+}
+
+int nbody_cuda_peer_detach_all(nbody_cuda_t h) {
+    if (!h) return NBODY_E_INVALID;
+    CU_TRY(h, cudaSetDevice(h->device));
+    if (h->stream) CU_TRY(h, cudaStreamSynchronize(h->stream));     // nothing of ours may still be storing into a peer
+    drop_peers(h);
     return NBODY_OK;
 }
 
@@ -1004,6 +1111,7 @@ struct NoAllocDevice {
     int sm_count = 0;
 };
 NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+std::mutex g_noalloc_mutex;      // guards the table above (set-up only; the launches themselves are not serialised)
 
 int noalloc_fail(char *err, size_t err_len, int code, const char *what, cudaError_t e = cudaSuccess) {
     if (err && err_len) {
@@ -1012,21 +1120,6 @@ int noalloc_fail(char *err, size_t err_len, int code, const char *what, cudaErro
     }
     if (e != cudaSuccess) cudaGetLastError();
     return code;
-}
-
-// Same choice as make_plan(), without a handle and without touching any buffer.
-int noalloc_pick_variant(size_t n, size_t n_slots, int sm_count, ForcePlan *plan) {
-    double best = 0.0;
-    int best_k = -1;
-    for (int k = 0; k < (int)(sizeof(kVariants) / sizeof(kVariants[0])); ++k) {
-        const ForcePlan p = plan_for(n, n_slots, sm_count, kVariants[k]);
-        const long long per_cta = (p.units + p.grid - 1) / p.grid;
-        const int resident = (p.grid + sm_count - 1) / sm_count;
-        const double t = (double)per_cta * resident * kVariants[k].I / kVariants[k].speed;
-        if (best_k < 0 || t < best) { best = t; best_k = k; }
-    }
-    *plan = plan_for(n, n_slots, sm_count, kVariants[best_k]);
-    return kVariants[best_k].I;
 }
 
 }  // namespace
@@ -1046,25 +1139,31 @@ extern "C" int nbody_cuda_accel_noalloc(const void *d_positions, void *d_acceler
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return noalloc_fail(err, err_len, NBODY_E_CUDA, "cudaGetDevice", e);
     if (dev < 0 || dev >= kNoAllocMaxDevices) return noalloc_fail(err, err_len, NBODY_E_INVALID, "device ordinal out of range");
-    NoAllocDevice &d = g_noalloc_dev[dev];
-    if (!d.ready) {
-        // One-time set-up on this device (it is the current one): in host code the name
-        // g_noalloc_scratch is only a stand-in for the symbol, not an address a kernel can use, so
-        // ask the runtime where the array lives on THIS GPU and hand that pointer to the kernels.
-        float4 *ptr = nullptr;
-        e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);
-        if (e != cudaSuccess || !ptr) return noalloc_fail(err, err_len, NBODY_E_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch)", e);
-        int sms = 0;
-        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e != cudaSuccess || sms <= 0) return noalloc_fail(err, err_len, NBODY_E_CUDA, "cudaDeviceGetAttribute(multiProcessorCount)", e);
-        d.scratch = ptr;
-        d.sm_count = sms;
-        d.ready = true;
+    NoAllocDevice d;
+    {
+        // One-time set-up per device, under a lock: two host threads may make the first call at once.
+        std::lock_guard<std::mutex> guard(g_noalloc_mutex);
+        NoAllocDevice &slot = g_noalloc_dev[dev];
+        if (!slot.ready) {
+            // This device is the current one.  In host code the name g_noalloc_scratch is only a
+            // stand-in for the symbol, not an address a kernel can use, so ask the runtime where the
+            // array lives on THIS GPU and hand that pointer to the kernels.
+            float4 *ptr = nullptr;
+            e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);
+            if (e != cudaSuccess || !ptr) return noalloc_fail(err, err_len, NBODY_E_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch)", e);
+            int sms = 0;
+            e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            if (e != cudaSuccess || sms <= 0) return noalloc_fail(err, err_len, NBODY_E_CUDA, "cudaDeviceGetAttribute(multiProcessorCount)", e);
+            slot.scratch = ptr;
+            slot.sm_count = sms;
+            slot.ready = true;
+        }
+        d = slot;
     }
     const size_t n_slots = (n + kTileJ - 1) / kTileJ * kTileJ;
-    ForcePlan plan;
-    const int I = noalloc_pick_variant(n, n_slots, d.sm_count, &plan);
-    const size_t need = ((size_t)plan.grid + plan.n_itiles) * kThreads * I;
+    ForcePlan plan;                    // same choice as make_plan(), without a handle and without touching any buffer
+    const int I = kVariants[pick_variant(n, n_slots, d.sm_count, 0, &plan)].I;
+    const size_t need = plan_partial_slots(plan);
     if (need > kNoAllocPartialSlots)
         return noalloc_fail(err, err_len, NBODY_E_INVALID, "this GPU's SM count needs more partial-sum scratch than the built-in array holds");
     cudaStream_t st = (cudaStream_t)stream;
@@ -1075,8 +1174,9 @@ extern "C" int nbody_cuda_accel_noalloc(const void *d_positions, void *d_acceler
     if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(err, err_len, NBODY_E_CUDA, "launch of stage_positions_kernel", e);
     ForceArgs a;
     a.pos = stage; a.partial = partial; a.n_local = (int)n; a.i_slot_begin = 0; a.eps2 = min_r2; a.plan = plan;
+    a.mask_self = !(min_r2 >= kMaskSelfBelowEps2);
     a.mass_info = nullptr;
-    launch_fast_variant<false>(I, plan.grid, st, a);      // mass_info is NULL: the general loop
+    launch_fast_variant<kLoopMassMul>(I, plan.grid, st, a);      // mass_info is NULL: the general loop
     if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(err, err_len, NBODY_E_CUDA, "launch of force_fast_kernel", e);
     reduce_partials_kernel<<<(int)((n + kThreads - 1) / kThreads), kThreads, 0, st>>>(partial, (int)n, kThreads * I, G, plan,
                                                                                       (float4 *)d_accelerations);

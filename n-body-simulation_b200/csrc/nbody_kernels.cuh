@@ -63,45 +63,107 @@ __device__ __forceinline__ float rsqrt_approx(float x) {
 // ---------------------------------------------------------------------------------------------
 // Work plan of the fast force kernel.
 //
-// The (target tile x source tile) rectangle is flattened into U = n_itiles * n_jtiles units;
-// CTA c of a persistent grid of G CTAs takes units [c*U/G, (c+1)*U/G): a run of consecutive
-// source tiles of one target tile, possibly continuing into the next target tile.  Every run
-// ("segment") leaves one partial sum per target in scratch slot (c + t); the finishing kernel
-// adds the segments of a target tile in ascending c, so the result does not depend on timing.
+// Targets are cut into tiles of 256*I targets (I targets per thread): n_main tiles of I_main, then
+// up to two narrower tail tiles (I in {4,2,1}) for the remainder, so that fewer than 256 padded
+// target rows are ever computed.  Each tile sweeps all n_slots sources, counted in granules of
+// kGran sources.  A granule of a tile with I targets per thread costs cost(I); the flattened
+// (tile, granule) sequence is cut into `grid` runs of equal COST, CTA c of a persistent grid
+// taking the granules [first_gran(c), first_gran(c+1)).  Inside one tile such a run is a
+// "segment"; every segment leaves one partial sum per target in scratch slot (c + t), and the
+// finishing kernel adds the segments of a tile in ascending c, so the result does not depend on
+// timing.  grid <= cost_total / max granule cost, hence no CTA is empty.
 // ---------------------------------------------------------------------------------------------
+constexpr int kGran = 16;          // sources per plan granule (8 packed pairs)
+constexpr int kMaxTail = 2;
+
+// which inner loop a force kernel runs
+constexpr int kLoopUnit = 0;       // all masses equal: m_j dropped from the loop (11 FMA-pipe ops per pair)
+constexpr int kLoopMassMul = 1;    // s = m_j / r^3 by an explicit multiply (12 ops per pair)
+
 struct ForcePlan {
-    long long units;   // U
-    int n_itiles;      // ceil(n_local / TI)
-    int n_jtiles;      // n_slots / kTileJ
-    int grid;          // G  (<= U, so no CTA is empty)
+    int n_gran;                 // granules per target tile = n_slots / kGran
+    int n_main;                 // target tiles of 256 * I_main targets
+    int n_tail;                 // 0..kMaxTail narrower tiles after them
+    int I_main;
+    int tail_I[kMaxTail];
+    int cost_main;
+    int cost_tail[kMaxTail];
+    int grid;                   // G
+    long long cost_total;       // C
 };
 
-__host__ __device__ __forceinline__ long long plan_first_unit(const ForcePlan &p, int c) {
-    return (long long)c * p.units / p.grid;
+// relative cost of one granule of a tile with I targets per thread.  Narrow tiles run well below the
+// rate of the I = 7 loop (fewer interactions per shared-memory read and per loop iteration); calibrated
+// on B200 so that the CTAs holding tail tiles finish with the others (gpurun_out/r2c_ab.log)
+__host__ __device__ __forceinline__ int plan_granule_cost(int I) { return I == 7 ? 73 : 10 * I + 7; }
+__host__ __device__ __forceinline__ int plan_tiles(const ForcePlan &p) { return p.n_main + p.n_tail; }
+__host__ __device__ __forceinline__ int plan_tile_I(const ForcePlan &p, int t) {
+    return t < p.n_main ? p.I_main : (t == p.n_main ? p.tail_I[0] : p.tail_I[1]);
 }
-// CTA that owns unit u: the largest c with floor(c*U/G) <= u.
-__host__ __device__ __forceinline__ int plan_owner(const ForcePlan &p, long long u) {
-    return (int)(((u + 1) * p.grid + p.units - 1) / p.units) - 1;
+// first local target of tile t
+__host__ __device__ __forceinline__ int plan_tile_target0(const ForcePlan &p, int t) {
+    if (t <= p.n_main) return t * kThreads * p.I_main;
+    return (p.n_main * p.I_main + p.tail_I[0]) * kThreads;      // second tail tile
+}
+// tile that holds local target l, and l's index inside it
+__host__ __device__ __forceinline__ void plan_tile_of_target(const ForcePlan &p, int l, int &t, int &r) {
+    const int TI = kThreads * p.I_main;
+    if (l < p.n_main * TI) { t = l / TI; r = l - t * TI; return; }
+    r = l - p.n_main * TI;
+    t = p.n_main;
+    if (p.n_tail == 2 && r >= kThreads * p.tail_I[0]) { r -= kThreads * p.tail_I[0]; t++; }
+}
+// cost position at which global granule g (= t * n_gran + granule within tile) starts; g may be the end
+__host__ __device__ __forceinline__ long long plan_cost_start(const ForcePlan &p, long long g) {
+    const long long main_gran = (long long)p.n_main * p.n_gran;
+    if (g <= main_gran) return g * p.cost_main;
+    long long c = main_gran * p.cost_main;
+    g -= main_gran;
+    if (g <= p.n_gran || p.n_tail < 2) return c + g * p.cost_tail[0];
+    return c + (long long)p.n_gran * p.cost_tail[0] + (g - p.n_gran) * p.cost_tail[1];
+}
+// granule that contains cost position pos (pos == cost_total: the end)
+__host__ __device__ __forceinline__ long long plan_gran_at(const ForcePlan &p, long long pos) {
+    const long long main_gran = (long long)p.n_main * p.n_gran;
+    const long long cm = main_gran * p.cost_main;
+    if (pos < cm) return pos / p.cost_main;
+    pos -= cm;
+    if (p.n_tail == 0) return main_gran;
+    const long long c0 = (long long)p.n_gran * p.cost_tail[0];
+    if (pos < c0) return main_gran + pos / p.cost_tail[0];
+    if (p.n_tail == 1) return main_gran + p.n_gran;
+    pos -= c0;
+    if (pos < (long long)p.n_gran * p.cost_tail[1]) return main_gran + p.n_gran + pos / p.cost_tail[1];
+    return main_gran + 2ll * p.n_gran;
+}
+__host__ __device__ __forceinline__ long long plan_first_gran(const ForcePlan &p, int c) {
+    return plan_gran_at(p, (long long)c * p.cost_total / p.grid);
+}
+// CTA that owns granule g: the largest c with first_gran(c) <= g
+__host__ __device__ __forceinline__ int plan_owner(const ForcePlan &p, long long g) {
+    return (int)((plan_cost_start(p, g + 1) * p.grid + p.cost_total - 1) / p.cost_total) - 1;
+}
+// scratch the plan needs, in float4
+__host__ __device__ __forceinline__ size_t plan_partial_slots(const ForcePlan &p) {
+    return ((size_t)p.grid + plan_tiles(p)) * kThreads * p.I_main;
 }
 
-#ifdef NBODY_TILE_INTERACT_OVERRIDE
-// tuning hook (tools/exp/tune_fast.cu): an experiment supplies its own tile_interact
-#include NBODY_TILE_INTERACT_OVERRIDE
-#else
-// One source tile against the I targets of this thread, packed two sources per instruction.
-// smem tile layout: A[q] = {x[2q], x[2q+1], y[2q], y[2q+1]},  B[q] = {z[2q], z[2q+1], m[2q], m[2q+1]}.
-// Per source pair and target: 3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 3 FMUL2 + 3 FFMA2.
-// kUnitMass: every source has the same mass, so m_j is dropped from the loop (11 FMA-pipe ops per
-// pair instead of 12) and applied once to the finished sum together with G.
-template <int I, bool kMaskSelf, bool kUnitMass>
+// One source tile (pairs [q0, q1), multiples of kGran / 2) against the I targets of this thread, packed two
+// sources per instruction.  smem tile layout: A[q] = {x[2q], x[2q+1], y[2q], y[2q+1]},
+// B[q] = {z[2q], z[2q+1], m[2q], m[2q+1]}.
+//   kLoopUnit     m unused.  3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 2 FMUL2 + 3 FFMA2 per source pair and target.
+//   kLoopMassMul  one more FMUL2 (s = m_j / r^3).
+// (Folding m_j into pre-scaled sources instead -- 11 operations for unequal masses too -- was measured 2.6 %
+// slower: its differences become three-operand FFMA2s; tools/exp/notes/scaled_sources_loop.md.)
+template <int I, bool kMaskSelf, int kLoop>
 __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, const float4 *__restrict__ sB,
                                               const u64 (&xi)[I], const u64 (&yi)[I], const u64 (&zi)[I],
                                               u64 eps2, u64 (&ax)[I], u64 (&ay)[I], u64 (&az)[I],
-                                              int tile_slot0, int self_slot0) {
-    // the self-containing tiles are unrolled like the others: in a small launch the CTA that owns
-    // them would otherwise finish last (N = 65 536: +1.4 % measured)
-#pragma unroll 2
-    for (int q = 0; q < kTileJ / 2; ++q) {
+                                              int q0, int q1, int tile_slot0, int self_slot0) {
+    // narrow tiles have too few independent chains per warp to cover the MUFU latency: unroll them further
+    constexpr int kUnrollQ = (I >= 4) ? 2 : (I == 2 ? 4 : 8);
+#pragma unroll kUnrollQ
+    for (int q = q0; q < q1; ++q) {
         const float4 a = sA[q];
         const float4 b = sB[q];
         const u64 xj = pack2(a.x, a.y), yj = pack2(a.z, a.w), zj = pack2(b.x, b.y), mj = pack2(b.z, b.w);
@@ -115,7 +177,7 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
             unpack2(r2, r2lo, r2hi);
             const u64 rinv = pack2(rsqrt_approx(r2lo), rsqrt_approx(r2hi));
             const u64 rinv2 = mul2(rinv, rinv);
-            u64 s = kUnitMass ? mul2(rinv2, rinv) : mul2(mul2(mj, rinv), rinv2);   // [m_j] / r^3
+            u64 s = (kLoop == kLoopMassMul) ? mul2(mul2(mj, rinv2), rinv) : mul2(rinv2, rinv);   // [m_j] / r^3
             if (kMaskSelf) {                       // the reference skips j == i by index
                 float slo, shi;
                 unpack2(s, slo, shi);
@@ -131,17 +193,98 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
     }
 }
 
-#endif  // NBODY_TILE_INTERACT_OVERRIDE
-
 struct ForceArgs {
     const float4 *pos;     // current global positions, n_slots
-    float4 *partial;       // scratch, (grid + n_itiles) * TI
+    float4 *partial;       // scratch, plan_partial_slots()
     int n_local;           // targets owned by this rank
     int i_slot_begin;      // slot of local target 0 (multiple of kSlotAlign)
     float eps2;            // SimParams::min_r2
+    int mask_self;         // skip j == i by index (needed only when the softening is too small, see below)
     ForcePlan plan;
     const unsigned *mass_info;   // {0 if all masses are equal, bits of that mass}; NULL: treat as unequal
 };
+
+// With softening the self term needs no mask: x_j - x_i is exactly 0 for j == i, so the term is
+// 0 * s with s = [m_j] (eps^2)^-3/2 finite -- it adds exactly nothing, as the reference's skip does.  The
+// masked tile variant costs 25 % more issue slots, and the I tiles that hold a tile's own targets sit
+// in one CTA's range, which made that CTA the last to finish in small systems.  Below this softening
+// (s could overflow to inf, 0 * inf = NaN; min_r2 = 0 is legal in the reference) the mask is kept.
+constexpr float kMaskSelfBelowEps2 = 1.0e-12f;
+
+constexpr int kBufFloats = (kTileJ / 2) * 4;     // floats per buffer of sA / sB
+
+// One segment: sources [src_begin, src_end) (multiples of kGran) against the tile of 256*I targets that
+// starts at local target `target0`; leaves the partial sums in out[0 .. 256*I).
+template <int I, int kLoop>
+__device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[kTileJ / 2], float4 (*sB)[kTileJ / 2],
+                                              float (*sOuter)[kThreads], int target0, int src_begin, int src_end,
+                                              float4 *__restrict__ out) {
+    const int tid = threadIdx.x;
+    const u64 eps2 = pack2(a.eps2, a.eps2);
+    // where this thread parks its source particle inside a packed tile
+    float *const stA0 = reinterpret_cast<float *>(&sA[0][tid >> 1]) + (tid & 1);
+    float *const stB0 = reinterpret_cast<float *>(&sB[0][tid >> 1]) + (tid & 1);
+
+    const int islot0 = a.i_slot_begin + target0;        // first target slot of this tile
+    u64 xi[I], yi[I], zi[I];
+    const int self_slot0 = islot0 + tid;                // target k of this thread sits in slot self_slot0 + 256 k
+#pragma unroll
+    for (int k = 0; k < I; ++k) {
+        const int l = target0 + k * kThreads + tid;     // local target index
+        const int slot = (l < a.n_local) ? islot0 + k * kThreads + tid : islot0;
+        const float4 p = a.pos[slot];
+        xi[k] = pack2(p.x, p.x);
+        yi[k] = pack2(p.y, p.y);
+        zi[k] = pack2(p.z, p.z);
+    }
+#pragma unroll
+    for (int k = 0; k < 3 * I; ++k) sOuter[k][tid] = 0.0f;   // private column: no barrier needed
+
+    const int diag0 = islot0 / kTileJ;                  // source tiles [diag0, diag0+I) hold the targets
+    const int jt0 = src_begin / kTileJ, jt_last = (src_end - 1) / kTileJ;
+    int buf = 0;
+    {
+        const float4 p = a.pos[jt0 * kTileJ + tid];
+        stA0[0] = p.x; stA0[2] = p.y; stB0[0] = p.z; stB0[2] = p.w;
+    }
+    __syncthreads();
+    u64 ax[I], ay[I], az[I];
+#pragma unroll
+    for (int k = 0; k < I; ++k) ax[k] = ay[k] = az[k] = 0ull;
+    for (int jt = jt0; jt <= jt_last; ++jt) {
+        float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool more = (jt < jt_last);
+        if (more) nxt = a.pos[(jt + 1) * kTileJ + tid];
+
+        const int q0 = (jt == jt0) ? (src_begin - jt * kTileJ) >> 1 : 0;
+        const int q1 = more ? kTileJ / 2 : (src_end - jt * kTileJ) >> 1;
+        const bool diag = a.mask_self && (jt >= diag0 && jt < diag0 + I);
+        if (diag) tile_interact<I, true, kLoop>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, q0, q1, jt * kTileJ, self_slot0);
+        else tile_interact<I, false, kLoop>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, q0, q1, jt * kTileJ, self_slot0);
+        // blocked summation: every kFlushTiles tiles (and at the end of the run) the inner
+        // accumulators are folded into the outer sums and restarted: 2048 terms per inner lane,
+        // N/4096 terms per outer sum -- neither level adds a long sequence
+        if ((((jt - jt0) & (kFlushTiles - 1)) == kFlushTiles - 1) || !more) {
+#pragma unroll
+            for (int k = 0; k < I; ++k) {
+                float lo, hi;
+                unpack2(ax[k], lo, hi); sOuter[3 * k + 0][tid] += lo + hi;
+                unpack2(ay[k], lo, hi); sOuter[3 * k + 1][tid] += lo + hi;
+                unpack2(az[k], lo, hi); sOuter[3 * k + 2][tid] += lo + hi;
+                ax[k] = ay[k] = az[k] = 0ull;
+            }
+        }
+        if (more) {
+            float *dA = stA0 + (buf ^ 1) * kBufFloats, *dB = stB0 + (buf ^ 1) * kBufFloats;
+            dA[0] = nxt.x; dA[2] = nxt.y; dB[0] = nxt.z; dB[2] = nxt.w;
+        }
+        __syncthreads();
+        buf ^= 1;
+    }
+#pragma unroll
+    for (int k = 0; k < I; ++k)
+        out[k * kThreads + tid] = make_float4(sOuter[3 * k][tid], sOuter[3 * k + 1][tid], sOuter[3 * k + 2][tid], 0.0f);
+}
 
 // Fast force kernel: persistent CTAs, I targets per thread in registers, source tiles staged
 // through double-buffered shared memory in the packed-pair layout, blocked summation (one
@@ -151,93 +294,36 @@ struct ForceArgs {
 // warps per scheduler consecutive instructions of a warp issue back to back, which keeps the
 // operand-reuse cache effective (the register file, not the FMA pipe, is the tighter resource
 // for FFMA2 with three distinct register pairs).
-// kUnitMass selects the loop at compile time (separate kernels keep each one's register allocation
-// tight); the launch that does not match the device-side mass flag returns at once, so the host can
-// enqueue both without knowing the flag.
-template <int I, bool kUnitMass>
+// kLoop selects the loop at compile time (separate kernels keep each one's register allocation
+// tight); a launch whose loop does not match the device-side mass flag returns at once, so the
+// host can enqueue the uniform-mass and the general kernel without knowing the flag.
+template <int I, int kLoop>
 __global__ void __launch_bounds__(kThreads, (I >= 4) ? 1 : 2) force_fast_kernel(const ForceArgs a) {
-    constexpr int TI = kThreads * I;
     __shared__ float4 sA[2][kTileJ / 2];
     __shared__ float4 sB[2][kTileJ / 2];
     __shared__ float sOuter[3 * I][kThreads];   // second level of the blocked sum, one column per thread
 
-    const int tid = threadIdx.x;
     const int c = blockIdx.x;
-    long long u = plan_first_unit(a.plan, c);
-    const long long u_end = plan_first_unit(a.plan, c + 1);
-    const u64 eps2 = pack2(a.eps2, a.eps2);
     const bool unit_mass = (a.mass_info != nullptr) && (a.mass_info[0] == 0u);   // grid-uniform
-    if (unit_mass != kUnitMass) return;
+    if (unit_mass != (kLoop == kLoopUnit)) return;
 
-    // where this thread parks its source particle inside a packed tile
-    float *const stA0 = reinterpret_cast<float *>(&sA[0][tid >> 1]) + (tid & 1);
-    float *const stB0 = reinterpret_cast<float *>(&sB[0][tid >> 1]) + (tid & 1);
-    constexpr int kBufFloats = (kTileJ / 2) * 4;
-
-    while (u < u_end) {
-        const int t = (int)(u / a.plan.n_jtiles);
-        const int jt0 = (int)(u - (long long)t * a.plan.n_jtiles);
-        const long long left = u_end - u;
-        const int jt1 = (a.plan.n_jtiles - jt0 < left) ? a.plan.n_jtiles : jt0 + (int)left;
-        u += jt1 - jt0;
-
-        const int islot0 = a.i_slot_begin + t * TI;        // first target slot of this tile
-        u64 xi[I], yi[I], zi[I];
-        const int self_slot0 = islot0 + tid;                // target k of this thread sits in slot self_slot0 + 256 k
-#pragma unroll
-        for (int k = 0; k < I; ++k) {
-            const int l = t * TI + k * kThreads + tid;      // local target index
-            const int slot = (l < a.n_local) ? islot0 + k * kThreads + tid : islot0;
-            const float4 p = a.pos[slot];
-            xi[k] = pack2(p.x, p.x);
-            yi[k] = pack2(p.y, p.y);
-            zi[k] = pack2(p.z, p.z);
-        }
-#pragma unroll
-        for (int k = 0; k < 3 * I; ++k) sOuter[k][tid] = 0.0f;   // private column: no barrier needed
-
-        const int diag0 = islot0 / kTileJ;                  // source tiles [diag0, diag0+I) hold the targets
-        int buf = 0;
-        {
-            const float4 p = a.pos[jt0 * kTileJ + tid];
-            stA0[0] = p.x; stA0[2] = p.y; stB0[0] = p.z; stB0[2] = p.w;
-        }
-        __syncthreads();
-        u64 ax[I], ay[I], az[I];
-#pragma unroll
-        for (int k = 0; k < I; ++k) ax[k] = ay[k] = az[k] = 0ull;
-        for (int jt = jt0; jt < jt1; ++jt) {
-            float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-            const bool more = (jt + 1 < jt1);
-            if (more) nxt = a.pos[(jt + 1) * kTileJ + tid];
-
-            const bool diag = (jt >= diag0 && jt < diag0 + I);
-            if (diag) tile_interact<I, true, kUnitMass>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot0);
-            else tile_interact<I, false, kUnitMass>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, jt * kTileJ, self_slot0);
-            // blocked summation: every kFlushTiles tiles (and at the end of the run) the inner
-            // accumulators are folded into the outer sums and restarted: 2048 terms per inner lane,
-            // N/4096 terms per outer sum -- neither level adds a long sequence
-            if ((((jt - jt0) & (kFlushTiles - 1)) == kFlushTiles - 1) || !more) {
-#pragma unroll
-                for (int k = 0; k < I; ++k) {
-                    float lo, hi;
-                    unpack2(ax[k], lo, hi); sOuter[3 * k + 0][tid] += lo + hi;
-                    unpack2(ay[k], lo, hi); sOuter[3 * k + 1][tid] += lo + hi;
-                    unpack2(az[k], lo, hi); sOuter[3 * k + 2][tid] += lo + hi;
-                    ax[k] = ay[k] = az[k] = 0ull;
-                }
-            }
-            if (more) {
-                float *dA = stA0 + (buf ^ 1) * kBufFloats, *dB = stB0 + (buf ^ 1) * kBufFloats;
-                dA[0] = nxt.x; dA[2] = nxt.y; dB[0] = nxt.z; dB[2] = nxt.w;
-            }
-            __syncthreads();
-            buf ^= 1;
-        }
+    long long g = plan_first_gran(a.plan, c);
+    const long long g_end = plan_first_gran(a.plan, c + 1);
+    const size_t TI = (size_t)kThreads * I;
+    while (g < g_end) {
+        const int t = (int)(g / a.plan.n_gran);
+        const int s0 = (int)(g - (long long)t * a.plan.n_gran);
+        const long long left = g_end - g;
+        const int run = (a.plan.n_gran - s0 < left) ? a.plan.n_gran - s0 : (int)left;
+        g += run;
+        const int It = plan_tile_I(a.plan, t);
+        const int target0 = plan_tile_target0(a.plan, t);
         float4 *out = a.partial + (size_t)(c + t) * TI;
-#pragma unroll
-        for (int k = 0; k < I; ++k)
-            out[k * kThreads + tid] = make_float4(sOuter[3 * k][tid], sOuter[3 * k + 1][tid], sOuter[3 * k + 2][tid], 0.0f);
+        const int sb = s0 * kGran, se = (s0 + run) * kGran;
+        if (It == I) force_segment<I, kLoop>(a, sA, sB, sOuter, target0, sb, se, out);
+        else if (I > 4 && It == 4) force_segment<(I > 4 ? 4 : 1), kLoop>(a, sA, sB, sOuter, target0, sb, se, out);
+        else if (I > 2 && It == 2) force_segment<(I > 2 ? 2 : 1), kLoop>(a, sA, sB, sOuter, target0, sb, se, out);
+        else force_segment<1, kLoop>(a, sA, sB, sOuter, target0, sb, se, out);
     }
 }
 
@@ -392,9 +478,10 @@ __global__ void __launch_bounds__(kThreads) finish_kernel(const FinishArgs a) {
     if (l < a.n_local) {
         float4 acc;
         if (kFromPartials) {
-            const int t = l / a.TI, r = l - t * a.TI;
-            const int c0 = plan_owner(a.plan, (long long)t * a.plan.n_jtiles);
-            const int c1 = plan_owner(a.plan, (long long)(t + 1) * a.plan.n_jtiles - 1);
+            int t, r;
+            plan_tile_of_target(a.plan, l, t, r);
+            const int c0 = plan_owner(a.plan, (long long)t * a.plan.n_gran);
+            const int c1 = plan_owner(a.plan, (long long)(t + 1) * a.plan.n_gran - 1);
             float sx = 0.0f, sy = 0.0f, sz = 0.0f;
             for (int c = c0; c <= c1; ++c) {
                 const float4 p = a.partial[(size_t)(c + t) * a.TI + r];
@@ -489,7 +576,7 @@ struct WaitArgs {
     int my_rank;
     int world;
     const unsigned *flags;   // own block: flags[r] = last barrier rank r has reached
-    unsigned *fault;         // own block: set to 1 + r if rank r never arrived
+    unsigned *fault;         // device alias of a page-locked host word: set to 1 + r if rank r never arrived
     unsigned long long timeout_ns;
 };
 __global__ void wait_kernel(const WaitArgs a) {
@@ -504,7 +591,8 @@ __global__ void wait_kernel(const WaitArgs a) {
         __nanosleep(200);
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         if (t - t0 > a.timeout_ns) {          // a peer died or fell out of step: give up instead of hanging the GPU
-            *a.fault = 1u + (unsigned)r;
+            *a.fault = 1u + (unsigned)r;          // host-mapped word: the host sees it without a stream operation
+            __threadfence_system();
             break;
         }
     } while (true);
@@ -847,9 +935,10 @@ __global__ void __launch_bounds__(kThreads) reduce_partials_kernel(const float4 
                                                                    float G, ForcePlan plan, float4 *__restrict__ acc) {
     const int l = blockIdx.x * kThreads + threadIdx.x;
     if (l >= n) return;
-    const int t = l / TI, r = l - t * TI;
-    const int c0 = plan_owner(plan, (long long)t * plan.n_jtiles);
-    const int c1 = plan_owner(plan, (long long)(t + 1) * plan.n_jtiles - 1);
+    int t, r;
+    plan_tile_of_target(plan, l, t, r);
+    const int c0 = plan_owner(plan, (long long)t * plan.n_gran);
+    const int c1 = plan_owner(plan, (long long)(t + 1) * plan.n_gran - 1);
     float sx = 0.0f, sy = 0.0f, sz = 0.0f;
     for (int c = c0; c <= c1; ++c) {           // same order as finish_kernel: ascending segment
         const float4 p = partial[(size_t)(c + t) * TI + r];

@@ -108,14 +108,29 @@ class CudaNaiveSimulation:
     def _ck(self, code: int) -> None:
         _lib.check(self._lib, self._h, code)
 
+    def _release_peers(self) -> None:
+        """COLLECTIVE (every rank of the group): unmap all peer blocks, then meet at a barrier, so that
+        no rank frees its exported block while another still has it open (CUDA IPC rule; the order
+        include/nbody_cuda.h documents for nbody_cuda_peer_detach_all)."""
+        if self.world > 1 and self._h.value:
+            self._ck(self._lib.nbody_cuda_peer_detach_all(self._h))
+            self._dist.barrier(group=self.group)
+
     def close(self) -> None:
+        """Frees the handle.  With a process group this is a COLLECTIVE call: every rank must close (the
+        ranks unmap one another's position blocks and meet at a barrier before any block is freed)."""
         if getattr(self, "_h", None) is not None and self._h.value:
+            self._release_peers()
             self._lib.nbody_cuda_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):
+        # garbage collection cannot be collective: unmap what this rank has open and free, without the barrier
         try:
-            self.close()
+            if getattr(self, "_h", None) is not None and self._h.value:
+                self._lib.nbody_cuda_peer_detach_all(self._h)
+                self._lib.nbody_cuda_destroy(self._h)
+                self._h = C.c_void_p()
         except Exception:
             pass
 
@@ -130,6 +145,8 @@ class CudaNaiveSimulation:
         """Declare the global particle count (collective when a group is set)."""
         if self.n_total == n_total:
             return
+        if self.n_total is not None:
+            self._release_peers()       # reconfiguring frees the exported block: peers let go of it first
         self._ck(self._lib.nbody_cuda_configure(self._h, n_total, self.rank, self.world))
         self.n_total = n_total
         self._pos_tensors = {}
@@ -290,6 +307,11 @@ class CudaNaiveSimulation:
         a, b, c, d = C.c_int(), C.c_int(), C.c_int(), C.c_int()
         self._ck(self._lib.nbody_cuda_plan(self._h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
         return dict(targets_per_thread=a.value, grid=b.value, target_tiles=c.value, source_tiles=d.value)
+
+    def set_option(self, name: str, value: int) -> None:
+        """"targets_per_thread" (0 auto, 1/2/4/7) or "barrier_timeout_ms" -- nbody_cuda_set_option."""
+        opt = {"targets_per_thread": _lib.OPT_TARGETS_PER_THREAD, "barrier_timeout_ms": _lib.OPT_BARRIER_TIMEOUT_MS}[name]
+        self._ck(self._lib.nbody_cuda_set_option(self._h, opt, int(value)))
 
     def launch_count(self) -> int:
         return int(self._lib.nbody_cuda_launch_count(self._h))

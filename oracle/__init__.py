@@ -146,6 +146,8 @@ class Reference:
             getattr(L, n).restype = d
         L.ref_mpi_naive_steps.argtypes = [vp, sz, f, f, f, i, i]
         L.ref_mpi_naive_steps.restype = d
+        L.ref_mpi_headless_loop.argtypes = [vp, sz, f, f, f, i, i]
+        L.ref_mpi_headless_loop.restype = d
         L.ref_checkpoint_begin.argtypes = [C.c_char_p, vp, sz, sz]
         L.ref_checkpoint_write_step.argtypes = [C.c_char_p, vp, sz]
         L.ref_checkpoint_read_header.argtypes = [C.c_char_p, vp]
@@ -206,6 +208,13 @@ class Reference:
         q = np.ascontiguousarray(p).copy()
         secs = self.lib.ref_mpi_naive_steps(_ptr(q), q.shape[0], G, dt, eps2, steps, nranks)
         return (q, secs) if timed else q
+
+    def mpi_headless_loop(self, p, G, dt, eps2, steps=1, nranks=1):
+        """(particles, seconds) with the reference's OWN definition of seconds for an MPI run: the headless
+        step loop with its per-step gather to rank 0 (src/apps/headless_main.cpp:344-421, --disable-output)."""
+        q = np.ascontiguousarray(p).copy()
+        secs = self.lib.ref_mpi_headless_loop(_ptr(q), q.shape[0], G, dt, eps2, steps, nranks)
+        return q, secs
 
     # checkpoint (trajectory) file
     def checkpoint_begin(self, path, p, target_steps):

@@ -249,6 +249,59 @@ double ref_mpi_naive_steps(void *particles, size_t n, float G, float dt, float m
     return *std::max_element(secs.begin(), secs.end());
 }
 
+// The reference's own definition of "seconds" for an MPI run (headless_main.cpp:344-421 with
+// --disable-output): barrier; clock; steps x { sim.step()  -- computeStep on the local slice plus
+// the render-buffer copy of Simulation.cpp:273-277 --  then MPI_Gatherv of every slice to rank 0 };
+// barrier; clock.  The gather is modelled as what a shared-memory MPI does: every rank copies its
+// 40-byte records into rank 0's buffer, rank 0 returns when all have arrived, the others return
+// at once (no extra synchronisation is charged to the CPU side).  Returns rank 0's wall time.
+double ref_mpi_headless_loop(void *particles, size_t n, float G, float dt, float min_r2, int steps, int nranks)
+{
+    if (nranks < 1) nranks = 1;
+    particle_t *all = static_cast<particle_t *>(particles);
+    std::vector<size_t> counts(nranks), displs(nranks);
+    const size_t base = n / nranks, rem = n % nranks;
+    for (int r = 0; r < nranks; ++r) counts[r] = base + ((size_t)r < rem ? 1 : 0);
+    displs[0] = 0;
+    for (int r = 1; r < nranks; ++r) displs[r] = displs[r - 1] + counts[r - 1];
+
+    ShimWorld world;
+    world.size = nranks;
+    world.bar = std::make_unique<std::barrier<>>(nranks);
+    world.boxes.resize(nranks);
+    g_world = &world;
+    CoutSilencer quiet;                              // once, on this thread: std::cout is shared by the thread-ranks
+    std::barrier<> gathered(nranks);                 // phase completes when every rank's slice is in the buffer
+    std::vector<particle_t> global_buffer(n);        // rank 0's receive buffer (headless_main.cpp:351-355)
+
+    double secs0 = 0.0;
+    auto body = [&](int r) {
+        t_rank = r;
+        SimParams p; p.G = G; p.dt = dt; p.min_r2 = min_r2;
+        NBodySimulation sim(std::make_unique<MpiNaiveSimulation>(), p);
+        sim.particles().assign(all + displs[r], all + displs[r] + counts[r]);
+        world.bar->arrive_and_wait();
+        auto t0 = std::chrono::steady_clock::now();
+        for (int s = 0; s < steps; ++s) {
+            sim.step();
+            if (counts[r]) std::memcpy(global_buffer.data() + displs[r], sim.particles().data(), counts[r] * sizeof(particle_t));
+            if (r == 0) gathered.arrive_and_wait();
+            else (void)gathered.arrive();
+        }
+        world.bar->arrive_and_wait();
+        auto t1 = std::chrono::steady_clock::now();
+        if (r == 0) secs0 = std::chrono::duration<double>(t1 - t0).count();
+    };
+    std::vector<std::thread> threads;
+    for (int r = 1; r < nranks; ++r) threads.emplace_back(body, r);
+    body(0);
+    for (auto &t : threads) t.join();
+    t_rank = 0;
+    g_world = nullptr;
+    if (n) std::memcpy(all, global_buffer.data(), n * sizeof(particle_t));
+    return secs0;
+}
+
 // ---------------------------------------------------------------------------
 // CheckpointManager (trajectory file)
 // ---------------------------------------------------------------------------

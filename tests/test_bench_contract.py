@@ -28,6 +28,9 @@ def test_reference_arm_line():
     assert d["value"] > 0 and d["vs_baseline"] is None and d["config"]["workload"].startswith("c4")
     assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert set(d["config"]) == {"workload", "n", "generator", "generator_source", "G", "dt", "min_r2", "l2"}
+    own = d["reference_own_clock"]          # the reference's own definition of seconds: step loop + per-step gather
+    assert own is None or (own["value"] > 0 and own["value"] <= d["value"] * 1.5)
 
 
 def test_reference_arm_other_ranks_exit_quietly():
@@ -59,3 +62,10 @@ def test_our_arm_line():
     cb = d["cpu_baseline"]
     assert cb["kind"] in ("reference", "port") and cb["cores"] == 1 and cb["value"] > 0
     assert "sm_mhz" in d["clocks"] and "reasons" in d["clocks"]
+    # the general (unequal-mass) loop is measured in the same run, by the same per-launch method
+    g = d["roofline_general"]
+    assert g["launches_timed"] >= 1 and 0.1 < g["frac"] < 1.0 and abs(g["frac"] - g["achieved"] / g["peak"]) < 1e-9
+    # both arms describe the workload with the same dictionary
+    r2, ref = run_bench("--impl", "reference", "--particles", "32768", "--steps", "1", "--warmup", "0", "--ref-n", "2048")
+    assert r2.returncode == 0 and ref["config"] == d["config"]
+    assert ref["reference_own_clock"]["ms_per_step"] > 0

@@ -26,7 +26,7 @@ def function_bodies(sass):
 def test_fast_kernels_are_packed_fp32(sass):
     bodies = function_bodies(sass)
     fast = {k: v for k, v in bodies.items() if "force_fast_kernel" in k}
-    assert len(fast) == 12                                   # I in {1,2,4,6,7,8} x {uniform mass, general}
+    assert len(fast) == 8                                    # I in {1,2,4,7} x {uniform mass, general}
     for name, body in fast.items():
         ops = re.findall(r"/\*[0-9a-f]{4,5}\*/\s+(?:@!?U?P\d\s+)?([A-Z0-9_]+)", body)
         assert ops.count("FFMA2") > 0 and ops.count("FADD2") > 0 and ops.count("FMUL2") > 0, name
@@ -63,4 +63,4 @@ def test_hot_kernels_do_not_spill():
             found += 1
             assert st == "0" and ld == "0", name            # the one-off generator kernel may keep its RNG state on the stack
             assert int(regs) <= 255
-    assert found >= 16
+    assert found >= 12

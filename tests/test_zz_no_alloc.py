@@ -31,19 +31,26 @@ def reference_path_acc(nb, p, G, eps2):
     return q["acceleration"]
 
 
-def call_noalloc(nb, torch, p, G, eps2):
+def call_noalloc(nb, torch, p, G, eps2, stream=None, in_place=False):
+    """One call through the C ABI.  `stream`: a torch.cuda.Stream to enqueue on (None: the default
+    stream).  `in_place`: hand the position buffer in as the output buffer too."""
     lib = nb.load_library()
     n = p.shape[0]
     xyzm = np.concatenate([p["position"], p["mass"][:, None]], axis=1).astype(np.float32)
     d_pos = torch.from_numpy(xyzm).cuda().contiguous()
-    d_acc = torch.full((max(n, 1), 4), float("nan"), dtype=torch.float32, device="cuda")
+    d_acc = d_pos if in_place else torch.full((max(n, 1), 4), float("nan"), dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
     err = C.create_string_buffer(256)
     rc = lib.nbody_cuda_accel_noalloc(C.c_void_p(d_pos.data_ptr()), C.c_void_p(d_acc.data_ptr()), n, G, eps2,
-                                      None, err, len(err))
+                                      C.c_void_p(stream.cuda_stream) if stream is not None else None, err, len(err))
     assert rc == 0, err.value
     torch.cuda.synchronize()
     return d_acc[:n, :3].cpu().numpy(), d_acc[:n, 3].cpu().numpy()
+
+
+def truth_acc(oracle, p, G, eps2):
+    """FP64 accelerations from the CPU oracle (oracle/nbody_oracle.c), the checker of this suite."""
+    return oracle.accel_f64(p, G, eps2)
 
 
 def test_noalloc_matches_existing_path_on_two_calls_in_a_row(nb):
@@ -59,6 +66,49 @@ def test_noalloc_matches_existing_path_on_two_calls_in_a_row(nb):
         want = reference_path_acc(nb, p, G, eps)
         assert np.isfinite(got).all() and np.all(w == 0)
         assert rel_err(got, want).max() < TOL
+
+
+def test_noalloc_against_the_oracle_on_a_side_stream_and_in_place(nb, oracle):
+    """The same two systems, checked against the FP64 CPU oracle rather than against this library's own
+    fast path; the first call is enqueued on a non-default stream, the second writes the accelerations
+    over the positions it was given (the sources are copied into the built-in array first)."""
+    import torch
+
+    torch.cuda.set_device(0)
+    G = 0.75
+    a, eps_a = nb.datasets.plummer_sphere(4099, seed=41)
+    a["mass"] = np.random.default_rng(9).uniform(0.5, 2.0, 4099).astype(np.float32)
+    b, eps_b = nb.datasets.galaxy_disk(2500, seed=42)
+    side = torch.cuda.Stream()
+    got_a, _ = call_noalloc(nb, torch, a, G, eps_a, stream=side)
+    got_b, w_b = call_noalloc(nb, torch, b, G, eps_b, in_place=True)
+    assert np.all(w_b == 0)
+    assert rel_err(got_a, truth_acc(oracle, a, G, eps_a)).max() < TOL
+    assert rel_err(got_b, truth_acc(oracle, b, G, eps_b)).max() < TOL
+
+
+def test_noalloc_really_allocates_nothing(nb):
+    """The property the entry point exists for: device memory in use is the same before and after a
+    call (cudaMemGetInfo through torch), once the first call on the device has done its look-up."""
+    import torch
+
+    torch.cuda.set_device(0)
+    p, eps = nb.datasets.plummer_sphere(3000, seed=43)
+    call_noalloc(nb, torch, p, 1.0, eps)                                # first call on the device: set-up
+    lib = nb.load_library()
+    xyzm = np.concatenate([p["position"], p["mass"][:, None]], axis=1).astype(np.float32)
+    d_pos = torch.from_numpy(xyzm).cuda().contiguous()
+    d_acc = torch.empty_like(d_pos)
+    err = C.create_string_buffer(256)
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info()
+    for _ in range(3):
+        rc = lib.nbody_cuda_accel_noalloc(C.c_void_p(d_pos.data_ptr()), C.c_void_p(d_acc.data_ptr()), 3000, 1.0, eps,
+                                          None, err, len(err))
+        assert rc == 0, err.value
+    torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info()
+    assert free_after == free_before
 
 
 def test_noalloc_limits_and_errors(nb):
