@@ -88,6 +88,17 @@ int nbody_cuda_download_aos(nbody_cuda_t h, void *particles, size_t count);
  * bytes per particle over PCIe. */
 int nbody_cuda_download_positions(nbody_cuda_t h, float *xyz, size_t count);
 
+/* The same record WITHOUT stopping the run (the reference writes a record every step,
+ * src/apps/headless_main.cpp:402-411, and its step loop waits for it).  _async packs the positions
+ * into one of two device staging buffers on the handle's stream and starts the copy to `xyz` on a
+ * separate copy stream, then returns: steps queued afterwards run while the record is still crossing
+ * PCIe.  `xyz` should be page-locked (nbody_cuda_host_alloc; with pageable memory the copy is not
+ * asynchronous) and must stay untouched until _wait returns.  At most two records are in flight --
+ * a third _async call makes the DEVICE wait for the oldest copy, not the host.  _wait blocks until
+ * every record requested so far has landed in host memory. */
+int nbody_cuda_download_positions_async(nbody_cuda_t h, float *xyz, size_t count);
+int nbody_cuda_download_positions_wait(nbody_cuda_t h);
+
 /* Fills the configured system with a synthetic particle set generated ON the device, instead of
  * nbody_cuda_upload_aos: the distributions of NBodySimulation::generatePlummerSphere
  * (src/Simulation.cpp:173-267; size_a = scale radius, size_b = total mass, < 0 for one per particle)
@@ -163,11 +174,17 @@ int nbody_cuda_plan_describe(size_t n_local, size_t n_slots, int sm_count, int t
 
 /* Tuning and diagnostic switches of a handle (no counterpart in the reference).
  *   NBODY_OPT_TARGETS_PER_THREAD  0 (default): the plan chooses; 1, 2, 4 or 7 forces the main tile width.
+ *   NBODY_OPT_RESIDENT_KERNEL     nbody_cuda_step on one GPU in fast mode can run all n_steps in ONE cooperative
+ *                                 launch (force and integrator phases separated by grid-wide barriers): 1 (default)
+ *                                 does so for systems of up to 12 288 particles, where the two kernel boundaries per
+ *                                 step otherwise cost more than the arithmetic; 0 never; 2 whenever the grid fits.
+ *                                 Results are bit-identical either way.
  *   NBODY_OPT_BARRIER_TIMEOUT_MS  how long the device-side wait for a peer's step counter may last before
  *                                 the run is reported as faulted (default 30 000); raise it for steps that
  *                                 take longer than that (strict / FP64 modes at very large N). */
 #define NBODY_OPT_TARGETS_PER_THREAD 2
 #define NBODY_OPT_BARRIER_TIMEOUT_MS 3
+#define NBODY_OPT_RESIDENT_KERNEL 4
 int nbody_cuda_set_option(nbody_cuda_t h, int option, long long value);
 
 /* Number of kernels this library has launched on the handle since creation. */

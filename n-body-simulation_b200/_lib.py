@@ -21,6 +21,7 @@ MODE_FP64 = 2
 PEER_HANDLE_BYTES = 128
 OPT_TARGETS_PER_THREAD = 2
 OPT_BARRIER_TIMEOUT_MS = 3
+OPT_RESIDENT_KERNEL = 4
 
 
 class NBodyCudaError(RuntimeError):
@@ -55,6 +56,8 @@ SIGNATURES = {
     "nbody_cuda_upload_aos": (_i, [_vp, _vp, _sz]),
     "nbody_cuda_download_aos": (_i, [_vp, _vp, _sz]),
     "nbody_cuda_download_positions": (_i, [_vp, _vp, _sz]),
+    "nbody_cuda_download_positions_async": (_i, [_vp, _vp, _sz]),
+    "nbody_cuda_download_positions_wait": (_i, [_vp]),
     "nbody_cuda_generate": (_i, [_vp, _i, _f, _f, _f, C.c_ulonglong, C.POINTER(_f)]),
     "nbody_cuda_render_frame": (_i, [_vp, _i, _i, _f, _f, _f, _vp]),
     "nbody_cuda_step": (_i, [_vp, _f, _f, _f, _i]),

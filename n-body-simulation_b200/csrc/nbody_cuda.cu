@@ -76,11 +76,23 @@ struct nbody_cuda {
     double *d_energy = nullptr;
     size_t energy_cap = 0;      // doubles
 
+    // asynchronous trajectory records: two staging buffers on the device, filled on the compute stream
+    // and drained to the caller's page-locked memory on a copy stream of their own
+    cudaStream_t copy_stream = nullptr;
+    float *rec_stage[2] = {nullptr, nullptr};
+    size_t rec_cap = 0;                              // floats per staging buffer
+    cudaEvent_t rec_packed[2] = {nullptr, nullptr};  // staging k holds the record (compute stream)
+    cudaEvent_t rec_copied[2] = {nullptr, nullptr};  // staging k has left for the host (copy stream)
+    bool rec_busy[2] = {false, false};
+    unsigned rec_count = 0;
+
     // fast-kernel plan
     int targets_per_thread = 4;
     ForcePlan plan{};
     int force_occupancy = 2;
     int forced_I = 0;                  // NBODY_OPT_TARGETS_PER_THREAD (0: chosen by the plan)
+    int resident_mode = 1;             // NBODY_OPT_RESIDENT_KERNEL: 0 never, 1 for small systems, 2 whenever possible
+    bool resident_fits = false;        // the plan's grid is co-resident for the cooperative launch
 
     // peers
     bool attached[kMaxWorld] = {false};
@@ -170,6 +182,11 @@ void free_buffers(nbody_cuda_t h) {
     if (h->partial) cudaFree(h->partial);
     if (h->d_aos) cudaFree(h->d_aos);
     if (h->d_energy) cudaFree(h->d_energy);
+    for (int k = 0; k < 2; ++k) {
+        if (h->rec_stage[k]) cudaFree(h->rec_stage[k]);
+        h->rec_stage[k] = nullptr; h->rec_busy[k] = false;
+    }
+    h->rec_cap = 0;
     h->block = nullptr; h->vel = h->acc = h->partial = nullptr; h->d_aos = nullptr; h->d_energy = nullptr;
     h->pos[0] = h->pos[1] = nullptr; h->flags = nullptr;
     h->block_bytes = h->local_cap = h->partial_cap = h->aos_cap = h->energy_cap = 0;
@@ -238,11 +255,14 @@ int pick_variant(size_t n_local, size_t n_slots, int sm_count, int forced_I, For
     return best_k;
 }
 
+bool resident_grid_fits(nbody_cuda_t h);
+
 // Chooses the variant with the smallest estimated time and sizes the partial-sum scratch.
 int make_plan(nbody_cuda_t h) {
     const int k = pick_variant(h->n_local, h->n_slots, h->sm_count, h->forced_I, &h->plan);
     h->targets_per_thread = kVariants[k].I;
     h->force_occupancy = kVariants[k].ctas_per_sm;
+    h->resident_fits = (h->world == 1) && resident_grid_fits(h);
     const size_t need = plan_partial_slots(h->plan);
     if (need > h->partial_cap) {
         if (h->partial) cudaFree(h->partial);
@@ -270,6 +290,48 @@ void launch_fast_variant(int I, int grid, cudaStream_t st, const ForceArgs &a) {
         case 2: force_fast_kernel<2, kLoop><<<grid, kThreads, 0, st>>>(a); break;
         default: force_fast_kernel<1, kLoop><<<grid, kThreads, 0, st>>>(a); break;
     }
+}
+
+// Largest system stepped by the resident (one cooperative launch for n_steps) kernel by default: above
+// this the grid barriers cost as much as the kernel boundaries they replace (measured cross-over near N = 15 000).
+constexpr size_t kResidentMaxN = 12288;
+
+template <int I, int kLoop>
+cudaError_t launch_resident_one(int grid, cudaStream_t st, ResidentArgs &a) {
+    void *params[] = {(void *)&a};
+    return cudaLaunchCooperativeKernel((const void *)resident_steps_kernel<I, kLoop>, dim3(grid), dim3(kThreads), params, 0, st);
+}
+template <int kLoop>
+cudaError_t launch_resident_variant(int I, int grid, cudaStream_t st, ResidentArgs &a) {
+    switch (I) {
+        case 7: return launch_resident_one<7, kLoop>(grid, st, a);
+        case 4: return launch_resident_one<4, kLoop>(grid, st, a);
+        case 2: return launch_resident_one<2, kLoop>(grid, st, a);
+        default: return launch_resident_one<1, kLoop>(grid, st, a);
+    }
+}
+template <int I>
+int resident_blocks_per_sm() {
+    int a = 0, b = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, resident_steps_kernel<I, kLoopUnit>, kThreads, 0) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, resident_steps_kernel<I, kLoopMassMul>, kThreads, 0) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return a < b ? a : b;
+}
+// Can every CTA of the plan be resident at once (the grid barrier of the resident kernel needs it)?
+bool resident_grid_fits(nbody_cuda_t h) {
+    int coop = 0;
+    if (cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device) != cudaSuccess || !coop) { cudaGetLastError(); return false; }
+    int per_sm = 0;
+    switch (h->targets_per_thread) {
+        case 7: per_sm = resident_blocks_per_sm<7>(); break;
+        case 4: per_sm = resident_blocks_per_sm<4>(); break;
+        case 2: per_sm = resident_blocks_per_sm<2>(); break;
+        default: per_sm = resident_blocks_per_sm<1>(); break;
+    }
+    return (long long)per_sm * h->sm_count >= h->plan.grid;
 }
 
 // Masses never change on the device, so one look after each upload (and after the exchange that
@@ -503,10 +565,16 @@ void nbody_cuda_destroy(nbody_cuda_t h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     free_buffers(h);
     for (auto &p : h->force_events) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     if (h->ev_begin) cudaEventDestroy(h->ev_begin);
     if (h->ev_end) cudaEventDestroy(h->ev_end);
+    for (int k = 0; k < 2; ++k) {
+        if (h->rec_packed[k]) cudaEventDestroy(h->rec_packed[k]);
+        if (h->rec_copied[k]) cudaEventDestroy(h->rec_copied[k]);
+    }
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->host_fault) cudaFreeHost((void *)h->host_fault);
     cudaGetLastError();
@@ -524,6 +592,8 @@ int nbody_cuda_configure(nbody_cuda_t h, size_t n_total, int rank, int world) {
     if (h->configured && n_total == h->n_total && rank == h->rank && world == h->world) return NBODY_OK;
 
     CU_TRY(h, cudaStreamSynchronize(h->stream));
+    if (h->copy_stream) CU_TRY(h, cudaStreamSynchronize(h->copy_stream));
+    h->rec_busy[0] = h->rec_busy[1] = false;
     drop_peers(h);          // tokens describe the old block
     drop_graph(h);          // so does a captured step
     size_t begin, count;
@@ -646,6 +716,58 @@ int nbody_cuda_download_positions(nbody_cuda_t h, float *xyz, size_t count) {
     return check_fault(h);
 }
 
+int nbody_cuda_download_positions_async(nbody_cuda_t h, float *xyz, size_t count) {
+    if (!h) return NBODY_E_INVALID;
+    if (!h->configured) return fail(h, NBODY_E_STATE, "nbody_cuda_download_positions_async: not configured");
+    if (count != h->n_local) return fail(h, NBODY_E_INVALID, "nbody_cuda_download_positions_async: count differs from the configured slice");
+    if (count && !xyz) return fail(h, NBODY_E_INVALID, "nbody_cuda_download_positions_async: xyz is NULL");
+    CU_TRY(h, cudaSetDevice(h->device));
+    if (count == 0) return NBODY_OK;
+    if (!h->copy_stream) {
+        CU_TRY(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) {
+            CU_TRY(h, cudaEventCreateWithFlags(&h->rec_packed[k], cudaEventDisableTiming));
+            CU_TRY(h, cudaEventCreateWithFlags(&h->rec_copied[k], cudaEventDisableTiming));
+        }
+    }
+    const size_t floats = count * 3;
+    if (floats > h->rec_cap) {
+        CU_TRY(h, cudaStreamSynchronize(h->copy_stream));          // nothing may still be draining the old buffers
+        for (int k = 0; k < 2; ++k) {
+            if (h->rec_stage[k]) cudaFree(h->rec_stage[k]);
+            h->rec_stage[k] = nullptr; h->rec_busy[k] = false;
+        }
+        h->rec_cap = 0;
+        for (int k = 0; k < 2; ++k) CU_TRY(h, cudaMalloc(&h->rec_stage[k], floats * sizeof(float)));
+        h->rec_cap = floats;
+    }
+    const int k = (int)(h->rec_count & 1u);
+    // staging k may still be on its way to the host (the record before last): the pack waits for that copy,
+    // on the device -- the host does not block
+    if (h->rec_busy[k]) CU_TRY(h, cudaStreamWaitEvent(h->stream, h->rec_copied[k], 0));
+    pack_positions_kernel<<<(int)((count + kThreads - 1) / kThreads), kThreads, 0, h->stream>>>(
+        h->rec_stage[k], (int)count, (int)(h->rank * h->slot_stride), h->pos[h->cur]);
+    CHECK_LAUNCH(h, "pack_positions_kernel");
+    CU_TRY(h, cudaEventRecord(h->rec_packed[k], h->stream));
+    CU_TRY(h, cudaStreamWaitEvent(h->copy_stream, h->rec_packed[k], 0));
+    CU_TRY(h, cudaMemcpyAsync(xyz, h->rec_stage[k], floats * sizeof(float), cudaMemcpyDeviceToHost, h->copy_stream));
+    CU_TRY(h, cudaEventRecord(h->rec_copied[k], h->copy_stream));
+    h->rec_busy[k] = true;
+    h->rec_count++;
+    return NBODY_OK;
+}
+
+int nbody_cuda_download_positions_wait(nbody_cuda_t h) {
+    if (!h) return NBODY_E_INVALID;
+    CU_TRY(h, cudaSetDevice(h->device));
+    for (int k = 0; k < 2; ++k) {
+        if (!h->rec_busy[k]) continue;
+        CU_TRY(h, cudaEventSynchronize(h->rec_copied[k]));
+        h->rec_busy[k] = false;
+    }
+    return report_fault(h);
+}
+
 int nbody_cuda_generate(nbody_cuda_t h, int kind, float size_a, float size_b, float G, unsigned long long seed, float *min_r2_out) {
     if (!h) return NBODY_E_INVALID;
     if (!h->configured) return fail(h, NBODY_E_STATE, "nbody_cuda_generate: call nbody_cuda_configure first");
@@ -740,6 +862,33 @@ int nbody_cuda_step(nbody_cuda_t h, float G, float dt, float min_r2, int n_steps
         return fail(h, NBODY_E_STATE, "nbody_cuda_step: world > 1 needs every peer attached (or use nbody_cuda_step_local + an all-gather)");
     if (report_fault(h) != NBODY_OK) return NBODY_E_CUDA;      // an earlier exchange timed out: do not step on stale positions
     CU_TRY(h, cudaSetDevice(h->device));
+    // small systems on one GPU: all n_steps in one cooperative launch (force and integrator phases
+    // separated by grid barriers instead of kernel boundaries)
+    const bool use_resident = h->world == 1 && h->mode == NBODY_MODE_FAST && !h->profile_force && h->n_local > 0 && n_steps > 0 &&
+                              h->resident_fits && (h->resident_mode == 2 || (h->resident_mode == 1 && h->n_total <= kResidentMaxN));
+    if (use_resident) {
+        int rc = ensure_mass_info(h);
+        if (rc != NBODY_OK) return rc;
+        ResidentArgs a;
+        a.pos[0] = h->pos[0]; a.pos[1] = h->pos[1]; a.vel = h->vel; a.acc = h->acc; a.partial = h->partial;
+        a.n = (int)h->n_local; a.cur = h->cur; a.n_steps = n_steps;
+        a.mask_self = !(min_r2 >= kMaskSelfBelowEps2);
+        a.eps2 = min_r2; a.G = G; a.dt = dt; a.plan = h->plan; a.mass_info = h->flags + kMassInfoWord;
+        CU_TRY(h, cudaEventRecord(h->ev_begin, h->stream));
+        // as in launch_force: until the host knows the mass flag both loops are enqueued, one returns at once
+        if (h->mass_state != 0) {
+            CU_TRY(h, launch_resident_variant<kLoopUnit>(h->targets_per_thread, h->plan.grid, h->stream, a));
+            h->launches++;
+        }
+        if (h->mass_state != 1) {
+            CU_TRY(h, launch_resident_variant<kLoopMassMul>(h->targets_per_thread, h->plan.grid, h->stream, a));
+            h->launches++;
+        }
+        h->cur ^= (n_steps & 1);
+        CU_TRY(h, cudaEventRecord(h->ev_end, h->stream));
+        h->timed = true;
+        return NBODY_OK;
+    }
     int done = 0;
     const bool use_graph = h->world == 1 && !h->profile_force && n_steps >= 4 && h->n_local > 0;
     if (use_graph) {
@@ -900,6 +1049,10 @@ int nbody_cuda_set_option(nbody_cuda_t h, int option, long long value) {
                 drop_graph(h);
                 return make_plan(h);
             }
+            return NBODY_OK;
+        case NBODY_OPT_RESIDENT_KERNEL:
+            if (value < 0 || value > 2) return fail(h, NBODY_E_INVALID, "nbody_cuda_set_option: resident kernel must be 0 (off), 1 (small systems) or 2 (always)");
+            h->resident_mode = (int)value;
             return NBODY_OK;
         case NBODY_OPT_BARRIER_TIMEOUT_MS:
             if (value < 1) return fail(h, NBODY_E_INVALID, "nbody_cuda_set_option: barrier time-out must be at least 1 ms");

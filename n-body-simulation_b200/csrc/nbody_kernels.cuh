@@ -13,6 +13,7 @@
 // Slot s = r * slot_stride + l holds local particle l of rank r; slots past a rank's count are
 // zero-mass padding parked far away, so they contribute exactly 0 to every sum.
 #pragma once
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <curand_kernel.h>
 #include <stdint.h>
@@ -232,7 +233,7 @@ __device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[k
     for (int k = 0; k < I; ++k) {
         const int l = target0 + k * kThreads + tid;     // local target index
         const int slot = (l < a.n_local) ? islot0 + k * kThreads + tid : islot0;
-        const float4 p = a.pos[slot];
+        const float4 p = __ldcg(a.pos + slot);          // .cg: see resident_steps_kernel
         xi[k] = pack2(p.x, p.x);
         yi[k] = pack2(p.y, p.y);
         zi[k] = pack2(p.z, p.z);
@@ -244,7 +245,7 @@ __device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[k
     const int jt0 = src_begin / kTileJ, jt_last = (src_end - 1) / kTileJ;
     int buf = 0;
     {
-        const float4 p = a.pos[jt0 * kTileJ + tid];
+        const float4 p = __ldcg(a.pos + jt0 * kTileJ + tid);
         stA0[0] = p.x; stA0[2] = p.y; stB0[0] = p.z; stB0[2] = p.w;
     }
     __syncthreads();
@@ -254,7 +255,7 @@ __device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[k
     for (int jt = jt0; jt <= jt_last; ++jt) {
         float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
         const bool more = (jt < jt_last);
-        if (more) nxt = a.pos[(jt + 1) * kTileJ + tid];
+        if (more) nxt = __ldcg(a.pos + (jt + 1) * kTileJ + tid);
 
         const int q0 = (jt == jt0) ? (src_begin - jt * kTileJ) >> 1 : 0;
         const int q1 = more ? kTileJ / 2 : (src_end - jt * kTileJ) >> 1;
@@ -298,15 +299,9 @@ __device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[k
 // tight); a launch whose loop does not match the device-side mass flag returns at once, so the
 // host can enqueue the uniform-mass and the general kernel without knowing the flag.
 template <int I, int kLoop>
-__global__ void __launch_bounds__(kThreads, (I >= 4) ? 1 : 2) force_fast_kernel(const ForceArgs a) {
-    __shared__ float4 sA[2][kTileJ / 2];
-    __shared__ float4 sB[2][kTileJ / 2];
-    __shared__ float sOuter[3 * I][kThreads];   // second level of the blocked sum, one column per thread
-
+__device__ __forceinline__ void force_phase(const ForceArgs &a, float4 (*sA)[kTileJ / 2], float4 (*sB)[kTileJ / 2],
+                                            float (*sOuter)[kThreads]) {
     const int c = blockIdx.x;
-    const bool unit_mass = (a.mass_info != nullptr) && (a.mass_info[0] == 0u);   // grid-uniform
-    if (unit_mass != (kLoop == kLoopUnit)) return;
-
     long long g = plan_first_gran(a.plan, c);
     const long long g_end = plan_first_gran(a.plan, c + 1);
     const size_t TI = (size_t)kThreads * I;
@@ -325,6 +320,17 @@ __global__ void __launch_bounds__(kThreads, (I >= 4) ? 1 : 2) force_fast_kernel(
         else if (I > 2 && It == 2) force_segment<(I > 2 ? 2 : 1), kLoop>(a, sA, sB, sOuter, target0, sb, se, out);
         else force_segment<1, kLoop>(a, sA, sB, sOuter, target0, sb, se, out);
     }
+}
+
+template <int I, int kLoop>
+__global__ void __launch_bounds__(kThreads, (I >= 4) ? 1 : 2) force_fast_kernel(const ForceArgs a) {
+    __shared__ float4 sA[2][kTileJ / 2];
+    __shared__ float4 sB[2][kTileJ / 2];
+    __shared__ float sOuter[3 * I][kThreads];   // second level of the blocked sum, one column per thread
+
+    const bool unit_mass = (a.mass_info != nullptr) && (a.mass_info[0] == 0u);   // grid-uniform
+    if (unit_mass != (kLoop == kLoopUnit)) return;
+    force_phase<I, kLoop>(a, sA, sB, sOuter);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -472,21 +478,52 @@ struct FinishArgs {
     int my_rank;
 };
 
+// The reference's semi-implicit Euler step, each product and sum rounded separately
+// (src/NaiveSimulation.cpp:47-50): v += a*dt; x += v*dt.
+__device__ __forceinline__ void integrate_one(float4 &p, float4 &v, const float4 acc, float dt) {
+    v.x = __fadd_rn(v.x, __fmul_rn(acc.x, dt));
+    v.y = __fadd_rn(v.y, __fmul_rn(acc.y, dt));
+    v.z = __fadd_rn(v.z, __fmul_rn(acc.z, dt));
+    p.x = __fadd_rn(p.x, __fmul_rn(v.x, dt));
+    p.y = __fadd_rn(p.y, __fmul_rn(v.y, dt));
+    p.z = __fadd_rn(p.z, __fmul_rn(v.z, dt));
+}
+
+// Sum of the segment partials of local target l, in ascending segment (CTA) order.  Small systems cut
+// a tile into dozens of segments (N = 4096: 37 per tile); reading them one dependent load at a time
+// made this the longest kernel of their step (14 us against 11 for the force kernel), so the loads are
+// issued sixteen at a time and added afterwards, in the same order as before.
+__device__ __forceinline__ void sum_segments(const float4 *__restrict__ partial, const ForcePlan &plan, int TI, int l,
+                                             float &sx, float &sy, float &sz) {
+    int t, r;
+    plan_tile_of_target(plan, l, t, r);
+    const int c0 = plan_owner(plan, (long long)t * plan.n_gran);
+    const int c1 = plan_owner(plan, (long long)(t + 1) * plan.n_gran - 1);
+    const float4 *src = partial + (size_t)(c0 + t) * TI + r;
+    sx = sy = sz = 0.0f;
+    constexpr int kBatch = 16;
+    for (int c = c0; c <= c1; c += kBatch) {
+        float4 v[kBatch];
+        const int last = c1 - c;                       // loads past the last segment re-read it (and are dropped)
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k) v[k] = __ldcg(src + (size_t)min(k, last) * TI);
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k) {
+            const bool live = k <= last;
+            sx += live ? v[k].x : 0.0f; sy += live ? v[k].y : 0.0f; sz += live ? v[k].z : 0.0f;
+        }
+        src += (size_t)kBatch * TI;
+    }
+}
+
 template <bool kFromPartials>
 __global__ void __launch_bounds__(kThreads) finish_kernel(const FinishArgs a) {
     const int l = blockIdx.x * kThreads + threadIdx.x;
     if (l < a.n_local) {
         float4 acc;
         if (kFromPartials) {
-            int t, r;
-            plan_tile_of_target(a.plan, l, t, r);
-            const int c0 = plan_owner(a.plan, (long long)t * a.plan.n_gran);
-            const int c1 = plan_owner(a.plan, (long long)(t + 1) * a.plan.n_gran - 1);
-            float sx = 0.0f, sy = 0.0f, sz = 0.0f;
-            for (int c = c0; c <= c1; ++c) {
-                const float4 p = a.partial[(size_t)(c + t) * a.TI + r];
-                sx += p.x; sy += p.y; sz += p.z;
-            }
+            float sx, sy, sz;
+            sum_segments(a.partial, a.plan, a.TI, l, sx, sy, sz);
             float scale = a.G;
             if (a.mass_info != nullptr && a.mass_info[0] == 0u) scale = a.G * __uint_as_float(a.mass_info[1]);
             acc = make_float4(scale * sx, scale * sy, scale * sz, 0.0f);
@@ -497,12 +534,7 @@ __global__ void __launch_bounds__(kThreads) finish_kernel(const FinishArgs a) {
         const int slot = a.i_slot_begin + l;
         float4 p = a.pos_cur[slot];
         float4 v = a.vel[l];
-        v.x = __fadd_rn(v.x, __fmul_rn(acc.x, a.dt));
-        v.y = __fadd_rn(v.y, __fmul_rn(acc.y, a.dt));
-        v.z = __fadd_rn(v.z, __fmul_rn(acc.z, a.dt));
-        p.x = __fadd_rn(p.x, __fmul_rn(v.x, a.dt));
-        p.y = __fadd_rn(p.y, __fmul_rn(v.y, a.dt));
-        p.z = __fadd_rn(p.z, __fmul_rn(v.z, a.dt));
+        integrate_one(p, v, acc, a.dt);
         a.vel[l] = v;
         a.pos_next[slot] = p;
         for (int q = 0; q < a.n_peers; ++q) a.peer_next[q][slot] = p;      // NVLink stores into each peer's array
@@ -522,6 +554,70 @@ __global__ void __launch_bounds__(kThreads) finish_kernel(const FinishArgs a) {
                     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flags[q] + a.my_rank), "r"(a.signal_seq) : "memory");
             }
         }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Resident stepping kernel for small systems on one GPU: n_steps whole steps in ONE cooperative
+// launch.  Below N ~ 30 000 a step is tens of microseconds of arithmetic, and two dependent kernels
+// per step cost about 12 us in launch, drain and first-touch latency whatever the size (measured:
+// N = 1024 takes 12.3 us per step under CUDA-graph replay).  Here the force phase and the integrator
+// phase of every step are separated by grid-wide barriers instead of kernel boundaries; the
+// arithmetic, the plan, the partial-sum layout and the order of every sum are those of
+// force_fast_kernel + finish_kernel, so the results are bit-identical to the two-kernel path.
+// Positions and partials written by other CTAs inside the launch are read with ld.global.cg (L2),
+// never through L1.
+// ---------------------------------------------------------------------------------------------
+struct ResidentArgs {
+    float4 *pos[2];        // double-buffered global positions
+    float4 *vel, *acc, *partial;
+    int n;                 // particles (single GPU: all targets are local, slot == index)
+    int cur;               // which position array is current on entry
+    int n_steps;
+    int mask_self;
+    float eps2, G, dt;
+    ForcePlan plan;
+    const unsigned *mass_info;
+};
+
+template <int I, int kLoop>
+__global__ void __launch_bounds__(kThreads, (I >= 4) ? 1 : 2) resident_steps_kernel(const ResidentArgs a) {
+    __shared__ float4 sA[2][kTileJ / 2];
+    __shared__ float4 sB[2][kTileJ / 2];
+    __shared__ float sOuter[3 * I][kThreads];
+
+    const bool unit_mass = (a.mass_info != nullptr) && (a.mass_info[0] == 0u);   // grid-uniform: all CTAs leave together
+    if (unit_mass != (kLoop == kLoopUnit)) return;
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const float scale = unit_mass ? a.G * __uint_as_float(a.mass_info[1]) : a.G;
+    const int TI = kThreads * I;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n_chunks = (a.n + 31) >> 5;                 // the integrator phase works in 32-target chunks,
+    int cur = a.cur;                                      // chunk k on warp (k / grid) of CTA (k % grid): every SM takes part
+    for (int s = 0; s < a.n_steps; ++s) {
+        ForceArgs fa;
+        fa.pos = a.pos[cur]; fa.partial = a.partial; fa.n_local = a.n; fa.i_slot_begin = 0; fa.eps2 = a.eps2;
+        fa.mask_self = a.mask_self; fa.plan = a.plan; fa.mass_info = a.mass_info;
+        force_phase<I, kLoop>(fa, sA, sB, sOuter);
+        grid.sync();                                      // every partial sum is written and visible
+        const float4 *pos_cur = a.pos[cur];
+        float4 *pos_next = a.pos[cur ^ 1];
+        for (int k = warp * (int)gridDim.x + (int)blockIdx.x; k < n_chunks; k += (kThreads / 32) * (int)gridDim.x) {
+            const int l = k * 32 + lane;
+            if (l < a.n) {
+                float sx, sy, sz;
+                sum_segments(a.partial, a.plan, TI, l, sx, sy, sz);
+                const float4 acc = make_float4(scale * sx, scale * sy, scale * sz, 0.0f);
+                float4 p = __ldcg(pos_cur + l);
+                float4 v = __ldcg(a.vel + l);
+                integrate_one(p, v, acc, a.dt);
+                a.acc[l] = acc;
+                a.vel[l] = v;
+                pos_next[l] = p;
+            }
+        }
+        grid.sync();                                      // the new positions are complete before anyone reads them
+        cur ^= 1;
     }
 }
 
@@ -935,15 +1031,8 @@ __global__ void __launch_bounds__(kThreads) reduce_partials_kernel(const float4 
                                                                    float G, ForcePlan plan, float4 *__restrict__ acc) {
     const int l = blockIdx.x * kThreads + threadIdx.x;
     if (l >= n) return;
-    int t, r;
-    plan_tile_of_target(plan, l, t, r);
-    const int c0 = plan_owner(plan, (long long)t * plan.n_gran);
-    const int c1 = plan_owner(plan, (long long)(t + 1) * plan.n_gran - 1);
-    float sx = 0.0f, sy = 0.0f, sz = 0.0f;
-    for (int c = c0; c <= c1; ++c) {           // same order as finish_kernel: ascending segment
-        const float4 p = partial[(size_t)(c + t) * TI + r];
-        sx += p.x; sy += p.y; sz += p.z;
-    }
+    float sx, sy, sz;
+    sum_segments(partial, plan, TI, l, sx, sy, sz);      // same order as finish_kernel: ascending segment
     acc[l] = make_float4(G * sx, G * sy, G * sz, 0.0f);
 }
 

@@ -112,7 +112,7 @@ class CudaNaiveSimulation:
         """COLLECTIVE (every rank of the group): unmap all peer blocks, then meet at a barrier, so that
         no rank frees its exported block while another still has it open (CUDA IPC rule; the order
         include/nbody_cuda.h documents for nbody_cuda_peer_detach_all)."""
-        if self.world > 1 and self._h.value:
+        if self.group is not None and self.world > 1 and self._h.value:
             self._ck(self._lib.nbody_cuda_peer_detach_all(self._h))
             self._dist.barrier(group=self.group)
 
@@ -247,6 +247,18 @@ class CudaNaiveSimulation:
         self._ck(self._lib.nbody_cuda_download_positions(self._h, out.ctypes.data_as(C.c_void_p), n))
         return out
 
+    def download_positions_async(self, out: np.ndarray) -> None:
+        """Start a trajectory record into `out` ((count, 3) float32, page-locked: PinnedArray) and return at
+        once; steps queued afterwards overlap the copy.  `out` is valid after wait_records()."""
+        n = self.slice()["count"]
+        if out.shape != (n, 3) or out.dtype != np.float32 or not out.flags["C_CONTIGUOUS"]:
+            raise ValueError(f"out must be a contiguous float32 array of shape ({n}, 3)")
+        self._ck(self._lib.nbody_cuda_download_positions_async(self._h, out.ctypes.data_as(C.c_void_p), n))
+
+    def wait_records(self) -> None:
+        """Block until every record started with download_positions_async has landed in host memory."""
+        self._ck(self._lib.nbody_cuda_download_positions_wait(self._h))
+
     def render_frame(self, width: int = 800, height: int = 600, camera_distance: float = 800.0,
                      angle_x: float = 0.0, angle_y: float = 0.0) -> np.ndarray:
         """(height, width, 3) uint8 frame of the device positions with the reference viewer's camera
@@ -309,8 +321,10 @@ class CudaNaiveSimulation:
         return dict(targets_per_thread=a.value, grid=b.value, target_tiles=c.value, source_tiles=d.value)
 
     def set_option(self, name: str, value: int) -> None:
-        """"targets_per_thread" (0 auto, 1/2/4/7) or "barrier_timeout_ms" -- nbody_cuda_set_option."""
-        opt = {"targets_per_thread": _lib.OPT_TARGETS_PER_THREAD, "barrier_timeout_ms": _lib.OPT_BARRIER_TIMEOUT_MS}[name]
+        """"targets_per_thread" (0 auto, 1/2/4/7), "barrier_timeout_ms" or "resident_kernel" (0 off, 1 small
+        systems, 2 always) -- nbody_cuda_set_option."""
+        opt = {"targets_per_thread": _lib.OPT_TARGETS_PER_THREAD, "barrier_timeout_ms": _lib.OPT_BARRIER_TIMEOUT_MS,
+               "resident_kernel": _lib.OPT_RESIDENT_KERNEL}[name]
         self._ck(self._lib.nbody_cuda_set_option(self._h, opt, int(value)))
 
     def launch_count(self) -> int:
@@ -320,6 +334,34 @@ class CudaNaiveSimulation:
         v = C.c_double()
         self._ck(self._lib.nbody_cuda_measure_fma_peak(self._h, int(packed), C.byref(v)))
         return v.value
+
+
+class PinnedArray:
+    """A page-locked NumPy array of the given shape and dtype (nbody_cuda_host_alloc), e.g. the
+    (count, 3) float32 landing buffer of an asynchronous trajectory record."""
+
+    def __init__(self, shape, dtype=np.float32):
+        self._lib = _lib.load_library()
+        self._ptr = C.c_void_p()
+        dt = np.dtype(dtype)
+        count = int(np.prod(shape))
+        nbytes = max(1, count) * dt.itemsize
+        _lib.check(self._lib, None, self._lib.nbody_cuda_host_alloc(C.byref(self._ptr), nbytes))
+        self._raw = (C.c_ubyte * nbytes).from_address(self._ptr.value)
+        self.array = np.frombuffer(self._raw, dtype=dt, count=count).reshape(shape)
+
+    def close(self) -> None:
+        if self._ptr is not None and self._ptr.value:
+            self.array = None
+            self._raw = None
+            self._lib.nbody_cuda_host_free(self._ptr)
+            self._ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class PinnedParticles:

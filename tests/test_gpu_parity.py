@@ -310,6 +310,32 @@ def test_uniform_mass_path_agrees_with_general_path(nb, oracle, fast):
     assert np.all(got_z["acceleration"] == 0)
 
 
+@pytest.mark.parametrize("kind,n", [("plummer", 1000), ("plummer", 4096), ("disk", 4099), ("disk", 10007), ("plummer", 20000)])
+def test_resident_kernel_equals_two_kernel_path_bitwise(nb, kind, n):
+    """Small systems run all n_steps in one cooperative launch (grid barriers instead of kernel
+    boundaries, csrc/nbody_kernels.cuh: resident_steps_kernel).  Same plan, same partial sums, same
+    order: every field must come out bit-identical to the force + finish kernel pair, for odd and
+    even step counts (the double-buffered position arrays end on either side)."""
+    p, eps = (nb.datasets.plummer_sphere if kind == "plummer" else nb.datasets.galaxy_disk)(n, seed=77)
+    params = nb.SimParams(1.0, 0.5, eps)
+    out = {}
+    for resident in (0, 2):
+        sim = nb.CudaNaiveSimulation(mode="fast")
+        sim.set_option("resident_kernel", resident)
+        q = p.copy()
+        sim.upload(q)
+        launches0 = sim.launch_count()
+        sim.step(params, 1); sim.step(params, 5); sim.step(params, 2)
+        launches = sim.launch_count() - launches0
+        sim.download(q)
+        k, u = sim.energy(params)
+        sim.close()
+        out[resident] = (q, launches, k + u)
+    assert same_bits(out[0][0], out[2][0])
+    assert out[0][2] == out[2][2]
+    assert out[2][1] < out[0][1]           # 3 calls -> at most 2 launches each, against 2 kernels per step
+
+
 def test_launch_counter_and_timers(nb, fast):
     p, eps = nb.datasets.plummer_sphere(8192, seed=1)
     fast.upload(p)
@@ -343,6 +369,44 @@ def test_trajectory_from_device_positions_matches_reference_writer(nb, reference
         q = reference.naive_steps(q, 1.0, 0.5, eps, 1)
         reference.checkpoint_write_step(theirs, q)
     assert open(ours, "rb").read() == open(theirs, "rb").read()
+
+
+def test_async_trajectory_records_equal_synchronous_ones(nb, reference, tmp_path):
+    """Records taken with download_positions_async (two staging buffers, copy stream; the next step is
+    queued before the record has left the device) build the same file, byte for byte, as the
+    synchronous path and as the reference's CheckpointManager -- also when three records are requested
+    back to back without waiting (the third makes the device, not the host, wait for the first)."""
+    n, steps = 3000, 7
+    p, eps = reference.disk(n, 78)
+    params = nb.SimParams(1.0, 0.5, eps)
+    files = {k: str(tmp_path / f"{k}.bin") for k in ("sync", "async", "ref")}
+    sim = nb.CudaNaiveSimulation(mode="strict")
+    # synchronous
+    w = nb.TrajectoryWriter(files["sync"], p["mass"], steps)
+    sim.upload(p.copy())
+    for _ in range(steps):
+        sim.step(params, 1)
+        w.write_step(sim.download_positions())
+    # asynchronous: every record is requested and the next step queued before anything is awaited
+    bufs = [nb.PinnedArray((n, 3)) for _ in range(steps)]
+    sim.upload(p.copy())
+    for k in range(steps):
+        sim.step(params, 1)
+        sim.download_positions_async(bufs[k].array)
+    sim.wait_records()
+    w = nb.TrajectoryWriter(files["async"], p["mass"], steps)
+    for b in bufs:
+        w.write_step(b.array)
+        b.close()
+    sim.close()
+    # the reference
+    reference.checkpoint_begin(files["ref"], p, steps)
+    q = p
+    for _ in range(steps):
+        q = reference.naive_steps(q, 1.0, 0.5, eps, 1)
+        reference.checkpoint_write_step(files["ref"], q)
+    data = {k: open(f, "rb").read() for k, f in files.items()}
+    assert data["async"] == data["sync"] == data["ref"]
 
 
 @pytest.mark.parametrize("mode", ["strict", "fast"])

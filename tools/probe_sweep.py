@@ -1,4 +1,4 @@
-"""Force-kernel sweep on one GPU: sizes x input kind x general-loop kind x forced targets per thread.
+"""Force-kernel sweep on one GPU: sizes x input kind x forced targets per thread.
 Device time of k resident steps (CUDA-graph replay), int/s and % of the FP32 FMA peak."""
 import sys, os, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -12,9 +12,8 @@ for n in sizes:
     for gen in ("plummer", "disk"):
         p, eps = (nb.datasets.galaxy_disk if gen == "disk" else nb.datasets.plummer_sphere)(n, seed=1)
         params = nb.SimParams(1.0, 0.5, eps)
-        for loop in ((0,) if gen == "plummer" else (0, 1)):
+        for loop in (0,):
             for I in widths:
-                sim.set_option("general_loop", loop)
                 sim.set_option("targets_per_thread", 0)
                 sim.upload(p)
                 sim.set_option("targets_per_thread", I)
@@ -25,6 +24,6 @@ for n in sizes:
                 for rep in range(3):
                     sim.step(params, steps); best = min(best, sim.last_step_ms())
                 rate = float(n) * n * steps / (best * 1e-3)
-                print(json.dumps({"n": n, "gen": gen, "loop": ["unit" if gen == "plummer" else "scaled", "massmul"][loop], "forced_I": I,
+                print(json.dumps({"n": n, "gen": gen, "loop": "unit" if gen == "plummer" else "general", "forced_I": I,
                                   "plan": sim.plan(), "steps": steps, "us_per_step": best / steps * 1e3, "int_per_s": rate,
                                   "pct_of_peak": 100 * rate / PEAK}), flush=True)
