@@ -149,14 +149,17 @@ __host__ __device__ __forceinline__ size_t plan_partial_slots(const ForcePlan &p
     return ((size_t)p.grid + plan_tiles(p)) * kThreads * p.I_main;
 }
 
-// One source tile (pairs [q0, q1), multiples of kGran / 2) against the I targets of this thread, packed two
-// sources per instruction.  smem tile layout: A[q] = {x[2q], x[2q+1], y[2q], y[2q+1]},
+// One source tile (all 128 pairs when kFullTile, else pairs [q0, q1), multiples of kGran / 2) against the I
+// targets of this thread, packed two sources per instruction.  The whole-tile form has compile-time
+// loop bounds on purpose: only then does ptxas keep the loop counter and the shared-memory addresses
+// in uniform registers; with bounds that come out of the plan arithmetic it falls back to vector
+// registers, whose reads compete with the FFMA2 operands (1.5 % slower, tools/sass_rf_model.py).  smem tile layout: A[q] = {x[2q], x[2q+1], y[2q], y[2q+1]},
 // B[q] = {z[2q], z[2q+1], m[2q], m[2q+1]}.
 //   kLoopUnit     m unused.  3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 2 FMUL2 + 3 FFMA2 per source pair and target.
 //   kLoopMassMul  one more FMUL2 (s = m_j / r^3).
 // (Folding m_j into pre-scaled sources instead -- 11 operations for unequal masses too -- was measured 2.6 %
 // slower: its differences become three-operand FFMA2s; tools/exp/notes/scaled_sources_loop.md.)
-template <int I, bool kMaskSelf, int kLoop>
+template <int I, bool kMaskSelf, int kLoop, bool kFullTile>
 __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, const float4 *__restrict__ sB,
                                               const u64 (&xi)[I], const u64 (&yi)[I], const u64 (&zi)[I],
                                               u64 eps2, u64 (&ax)[I], u64 (&ay)[I], u64 (&az)[I],
@@ -164,16 +167,27 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
     // narrow tiles have too few independent chains per warp to cover the MUFU latency: unroll them further
     constexpr int kUnrollQ = (I >= 4) ? 2 : (I == 2 ? 4 : 8);
 #pragma unroll kUnrollQ
-    for (int q = q0; q < q1; ++q) {
+    for (int q = kFullTile ? 0 : q0; q < (kFullTile ? kTileJ / 2 : q1); ++q) {
         const float4 a = sA[q];
         const float4 b = sB[q];
         const u64 xj = pack2(a.x, a.y), yj = pack2(a.z, a.w), zj = pack2(b.x, b.y), mj = pack2(b.z, b.w);
 #pragma unroll
         for (int k = 0; k < I; ++k) {
             const u64 dx = sub2(xj, xi[k]), dy = sub2(yj, yi[k]), dz = sub2(zj, zi[k]);
-            u64 r2 = fma2(dx, dx, eps2);
-            r2 = fma2(dy, dy, r2);
-            r2 = fma2(dz, dz, r2);
+            // The order in which the three squares and the three accumulations are written changes nothing
+            // arithmetically worth mentioning, but it changes ptxas's schedule, and the schedules differ by up to
+            // 4 % on the hardware (MUFU results consumed too early at the loop end).  Each loop uses the order that
+            // measured fastest in a 68-variant sweep on B200 (gpurun_out/r2k_matrix.log, r2l_matrix.log).
+            u64 r2;
+            if (kLoop == kLoopMassMul) {
+                r2 = fma2(dy, dy, eps2);
+                r2 = fma2(dx, dx, r2);
+                r2 = fma2(dz, dz, r2);
+            } else {
+                r2 = fma2(dx, dx, eps2);
+                r2 = fma2(dy, dy, r2);
+                r2 = fma2(dz, dz, r2);
+            }
             float r2lo, r2hi;
             unpack2(r2, r2lo, r2hi);
             const u64 rinv = pack2(rsqrt_approx(r2lo), rsqrt_approx(r2hi));
@@ -187,9 +201,15 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
                 shi = (j0 + 1 == self) ? 0.0f : shi;
                 s = pack2(slo, shi);
             }
-            ax[k] = fma2(dx, s, ax[k]);
-            ay[k] = fma2(dy, s, ay[k]);
-            az[k] = fma2(dz, s, az[k]);
+            if (kLoop == kLoopMassMul) {
+                az[k] = fma2(dz, s, az[k]);
+                ay[k] = fma2(dy, s, ay[k]);
+                ax[k] = fma2(dx, s, ax[k]);
+            } else {
+                ax[k] = fma2(s, dx, ax[k]);
+                ay[k] = fma2(s, dy, ay[k]);
+                az[k] = fma2(s, dz, az[k]);
+            }
         }
     }
 }
@@ -242,30 +262,53 @@ __device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[k
     for (int k = 0; k < 3 * I; ++k) sOuter[k][tid] = 0.0f;   // private column: no barrier needed
 
     const int diag0 = islot0 / kTileJ;                  // source tiles [diag0, diag0+I) hold the targets
-    const int jt0 = src_begin / kTileJ, jt_last = (src_end - 1) / kTileJ;
+    // The run is a partial first tile (head), whole tiles, and a partial last tile (tail).  Head and
+    // tail are peeled out of the tile loop so that the loop body keeps compile-time bounds; they go
+    // through the masked variant (correct for any tile, and they are at most two per segment).
+    const int jt_first = src_begin / kTileJ, jt_last = (src_end - 1) / kTileJ;
+    const int hq0 = (src_begin - jt_first * kTileJ) >> 1;            // first pair of the first tile
+    const int tq1 = (src_end - jt_last * kTileJ) >> 1;               // end pair of the last tile
+    // (measured: the general loop gains 1.5 % from the peeled form, the uniform-mass loop loses 3 % -- it keeps
+    // head and tail inside the loop, as run-time bounds of the same code)
+    constexpr bool kPeel = (kLoop == kLoopMassMul);
+    const bool has_head = kPeel && ((hq0 != 0) || (jt_first == jt_last && tq1 != kTileJ / 2));
+    const bool has_tail = kPeel && (jt_first != jt_last) && (tq1 != kTileJ / 2);
+    const int jtA = jt_first + (has_head ? 1 : 0), jtB = jt_last + 1 - (has_tail ? 1 : 0);   // whole tiles [jtA, jtB)
     int buf = 0;
     {
-        const float4 p = __ldcg(a.pos + jt0 * kTileJ + tid);
+        const float4 p = __ldcg(a.pos + jt_first * kTileJ + tid);
         stA0[0] = p.x; stA0[2] = p.y; stB0[0] = p.z; stB0[2] = p.w;
     }
     __syncthreads();
     u64 ax[I], ay[I], az[I];
 #pragma unroll
     for (int k = 0; k < I; ++k) ax[k] = ay[k] = az[k] = 0ull;
-    for (int jt = jt0; jt <= jt_last; ++jt) {
+    if (has_head) {
+        float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool more = (jt_first < jt_last);
+        if (more) nxt = __ldcg(a.pos + (jt_first + 1) * kTileJ + tid);
+        tile_interact<I, true, kLoop, false>(sA[0], sB[0], xi, yi, zi, eps2, ax, ay, az, hq0, (jt_first == jt_last) ? tq1 : kTileJ / 2,
+                                              jt_first * kTileJ, self_slot0);
+        if (more) {
+            float *dA = stA0 + kBufFloats, *dB = stB0 + kBufFloats;
+            dA[0] = nxt.x; dA[2] = nxt.y; dB[0] = nxt.z; dB[2] = nxt.w;
+        }
+        __syncthreads();
+        buf = 1;
+    }
+    for (int jt = jtA; jt < jtB; ++jt) {
         float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
         const bool more = (jt < jt_last);
         if (more) nxt = __ldcg(a.pos + (jt + 1) * kTileJ + tid);
 
-        const int q0 = (jt == jt0) ? (src_begin - jt * kTileJ) >> 1 : 0;
-        const int q1 = more ? kTileJ / 2 : (src_end - jt * kTileJ) >> 1;
         const bool diag = a.mask_self && (jt >= diag0 && jt < diag0 + I);
-        if (diag) tile_interact<I, true, kLoop>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, q0, q1, jt * kTileJ, self_slot0);
-        else tile_interact<I, false, kLoop>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, q0, q1, jt * kTileJ, self_slot0);
+        const int q0 = (jt == jt_first) ? hq0 : 0, q1 = (jt == jt_last) ? tq1 : kTileJ / 2;     // whole tile when peeled
+        if (diag) tile_interact<I, true, kLoop, kPeel>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, q0, q1, jt * kTileJ, self_slot0);
+        else tile_interact<I, false, kLoop, kPeel>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, q0, q1, jt * kTileJ, self_slot0);
         // blocked summation: every kFlushTiles tiles (and at the end of the run) the inner
         // accumulators are folded into the outer sums and restarted: 2048 terms per inner lane,
         // N/4096 terms per outer sum -- neither level adds a long sequence
-        if ((((jt - jt0) & (kFlushTiles - 1)) == kFlushTiles - 1) || !more) {
+        if (((jt - jtA) & (kFlushTiles - 1)) == kFlushTiles - 1) {
 #pragma unroll
             for (int k = 0; k < I; ++k) {
                 float lo, hi;
@@ -281,6 +324,17 @@ __device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[k
         }
         __syncthreads();
         buf ^= 1;
+    }
+    if (has_tail) {
+        tile_interact<I, true, kLoop, false>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, 0, tq1, jt_last * kTileJ, self_slot0);
+        __syncthreads();                                 // the next segment restages buffer 0
+    }
+#pragma unroll
+    for (int k = 0; k < I; ++k) {                        // what is left in the inner accumulators
+        float lo, hi;
+        unpack2(ax[k], lo, hi); sOuter[3 * k + 0][tid] += lo + hi;
+        unpack2(ay[k], lo, hi); sOuter[3 * k + 1][tid] += lo + hi;
+        unpack2(az[k], lo, hi); sOuter[3 * k + 2][tid] += lo + hi;
     }
 #pragma unroll
     for (int k = 0; k < I; ++k)

