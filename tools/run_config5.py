@@ -2,11 +2,11 @@
 records written through the reference's UNMODIFIED CheckpointManager (oracle/_ref), read back and
 compared bit for bit, and the FP64 energy tracked at every record.
 
-    torchrun --nproc-per-node 8 tools/run_config5.py [--n 4194304 --steps 1000 --every 100]
+    torchrun --nproc-per-node 8 tools/run_config5.py [--particles 4194304 --steps 1000 --every 100 --mode fast|fp64]
 
 This is a measurement/validation script (it may use oracle/_ref as the checker and as the
 reference's checkpoint writer); the product path is nbody_b200.CudaNaiveSimulation.
-Weak-scaling series (N^2/P constant): N(P) = 4,194,304 * sqrt(P/8) -> use --n with --gpus P.
+Weak-scaling series (N^2/P constant): N(P) = 4,194,304 * sqrt(P/8) -> use --particles with P ranks.
 """
 import argparse
 import json
@@ -39,11 +39,13 @@ def all_positions(sim, lib, n, world):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=4194304)
+    ap.add_argument("--particles", type=int, default=4194304, help="not --n: torchrun would read that as one of its own options")
     ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--every", type=int, default=100)
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "config5.json"))
     ap.add_argument("--traj", default="/tmp/config5_simulation_output.bin")
+    ap.add_argument("--mode", default="fast", choices=["fast", "strict", "fp64"],
+                    help="fp64: forces summed in double -- the yardstick the fast run's energy drift is compared with")
     args = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -51,12 +53,13 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
         group = dist.group.WORLD
-    n = args.n
+    n = args.particles
     p, eps = nb.datasets.plummer_sphere(n, 100.0, float(n), seed=12345)
     params = nb.SimParams(1.0, 0.5, eps)
     counts, displs = nb.slice_counts(n, world)
     lo, cnt = displs[rank], counts[rank]
-    sim = nb.CudaNaiveSimulation(device=local, mode="fast", group=group, exchange="p2p")
+    sim = nb.CudaNaiveSimulation(device=local, mode=args.mode, group=group, exchange="p2p")
+    sim.set_option("barrier_timeout_ms", 120000)
     lib = nb.load_library()
     sim.upload(p[lo:lo + cnt].copy(), n_total=n)
 
@@ -99,7 +102,7 @@ def main():
     wall = time.time() - t_start
     if rank == 0:
         rate = float(n) * n / (np.mean(step_ms) * 1e-3)
-        res = dict(n=n, gpus=world, steps=args.steps, every=args.every, min_r2=eps, ms_per_step=float(np.mean(step_ms)),
+        res = dict(mode=args.mode, n=n, gpus=world, steps=args.steps, every=args.every, min_r2=eps, ms_per_step=float(np.mean(step_ms)),
                    interactions_per_s=rate, wall_s=wall, energies=energies, records=records,
                    drift=(energies[-1][1] + energies[-1][2] - k0 - u0) / abs(k0 + u0),
                    trajectory_bytes=os.path.getsize(args.traj) if ref is not None else None,
