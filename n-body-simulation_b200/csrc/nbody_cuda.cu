@@ -238,7 +238,7 @@ double plan_estimate(const ForcePlan &p, int sm_count) {
     const double per_tile = (double)p.n_gran * max_cost;
     const double segments = 1.0 + share / per_tile;
     const int resident = (p.grid + sm_count - 1) / sm_count;     // CTAs sharing an SM split its FMA pipe
-    return (share + max_cost + segments * (26.0 + 2.0 * p.I_main)) * resident;
+    return (share + max_cost + segments * (10.0 + 14.0 * p.I_main)) * resident;
 }
 
 int pick_variant(size_t n_local, size_t n_slots, int sm_count, int forced_I, ForcePlan *plan) {
@@ -257,9 +257,24 @@ int pick_variant(size_t n_local, size_t n_slots, int sm_count, int forced_I, For
 
 bool resident_grid_fits(nbody_cuda_t h);
 
+// Largest system stepped by the resident (one cooperative launch for n_steps) kernel by default: above
+// this the grid barriers cost as much as the kernel boundaries they replace (measured cross-over near N = 15 000).
+constexpr size_t kResidentMaxN = 12288;
+
 // Chooses the variant with the smallest estimated time and sizes the partial-sum scratch.
 int make_plan(nbody_cuda_t h) {
-    const int k = pick_variant(h->n_local, h->n_slots, h->sm_count, h->forced_I, &h->plan);
+    // Systems that the resident kernel steps (one GPU, N <= kResidentMaxN) measured faster with 1024-target
+    // tiles than with 1792-target ones from N ~ 6000 up (N = 8192: 29.9 vs 32.9 us per step, N = 10 000:
+    // 43.0 vs 47.2; profiles/r2_small_n_sweep.log): less to load, clear and write per segment, and every
+    // CTA is in several segments there.  The cost estimate does not see that, so the width is capped here.
+    int width = h->forced_I;
+    if (width == 0 && h->world == 1 && h->n_total <= kResidentMaxN) width = (h->n_total > 3000) ? 4 : 0;
+    int k = pick_variant(h->n_local, h->n_slots, h->sm_count, width, &h->plan);
+    if (width == 4 && h->forced_I == 0) {                   // ... but never against a narrower choice of the estimate
+        ForcePlan free_plan;
+        const int kf = pick_variant(h->n_local, h->n_slots, h->sm_count, 0, &free_plan);
+        if (kVariants[kf].I < 4) { k = kf; h->plan = free_plan; }
+    }
     h->targets_per_thread = kVariants[k].I;
     h->force_occupancy = kVariants[k].ctas_per_sm;
     h->resident_fits = (h->world == 1) && resident_grid_fits(h);
@@ -291,10 +306,6 @@ void launch_fast_variant(int I, int grid, cudaStream_t st, const ForceArgs &a) {
         default: force_fast_kernel<1, kLoop><<<grid, kThreads, 0, st>>>(a); break;
     }
 }
-
-// Largest system stepped by the resident (one cooperative launch for n_steps) kernel by default: above
-// this the grid barriers cost as much as the kernel boundaries they replace (measured cross-over near N = 15 000).
-constexpr size_t kResidentMaxN = 12288;
 
 template <int I, int kLoop>
 cudaError_t launch_resident_one(int grid, cudaStream_t st, ResidentArgs &a) {
