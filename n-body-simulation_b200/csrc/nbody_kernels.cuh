@@ -158,7 +158,7 @@ __host__ __device__ __forceinline__ size_t plan_partial_slots(const ForcePlan &p
 //   kLoopUnit     m unused.  3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 2 FMUL2 + 3 FFMA2 per source pair and target.
 //   kLoopMassMul  one more FMUL2 (s = m_j / r^3).
 // (Folding m_j into pre-scaled sources instead -- 11 operations for unequal masses too -- was measured 2.6 %
-// slower: its differences become three-operand FFMA2s; tools/exp/notes/scaled_sources_loop.md.)
+// slower: its differences become three-operand FFMA2s; tools/exp/notes/tried_and_not_kept.md.)
 template <int I, bool kMaskSelf, int kLoop, bool kFullTile>
 __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, const float4 *__restrict__ sB,
                                               const u64 (&xi)[I], const u64 (&yi)[I], const u64 (&zi)[I],
