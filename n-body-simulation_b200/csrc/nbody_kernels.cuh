@@ -263,8 +263,7 @@ __device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[k
 
     const int diag0 = islot0 / kTileJ;                  // source tiles [diag0, diag0+I) hold the targets
     // The run is a partial first tile (head), whole tiles, and a partial last tile (tail).  Head and
-    // tail are peeled out of the tile loop so that the loop body keeps compile-time bounds; they go
-    // through the masked variant (correct for any tile, and they are at most two per segment).
+    // tail are peeled out of the tile loop so that the loop body keeps compile-time bounds.
     const int jt_first = src_begin / kTileJ, jt_last = (src_end - 1) / kTileJ;
     const int hq0 = (src_begin - jt_first * kTileJ) >> 1;            // first pair of the first tile
     const int tq1 = (src_end - jt_last * kTileJ) >> 1;               // end pair of the last tile
@@ -287,8 +286,11 @@ __device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[k
         float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
         const bool more = (jt_first < jt_last);
         if (more) nxt = __ldcg(a.pos + (jt_first + 1) * kTileJ + tid);
-        tile_interact<I, true, kLoop, false>(sA[0], sB[0], xi, yi, zi, eps2, ax, ay, az, hq0, (jt_first == jt_last) ? tq1 : kTileJ / 2,
-                                              jt_first * kTileJ, self_slot0);
+        const int hq1 = (jt_first == jt_last) ? tq1 : kTileJ / 2;
+        if (a.mask_self && jt_first >= diag0 && jt_first < diag0 + I)
+            tile_interact<I, true, kLoop, false>(sA[0], sB[0], xi, yi, zi, eps2, ax, ay, az, hq0, hq1, jt_first * kTileJ, self_slot0);
+        else
+            tile_interact<I, false, kLoop, false>(sA[0], sB[0], xi, yi, zi, eps2, ax, ay, az, hq0, hq1, jt_first * kTileJ, self_slot0);
         if (more) {
             float *dA = stA0 + kBufFloats, *dB = stB0 + kBufFloats;
             dA[0] = nxt.x; dA[2] = nxt.y; dB[0] = nxt.z; dB[2] = nxt.w;
@@ -326,7 +328,10 @@ __device__ __forceinline__ void force_segment(const ForceArgs &a, float4 (*sA)[k
         buf ^= 1;
     }
     if (has_tail) {
-        tile_interact<I, true, kLoop, false>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, 0, tq1, jt_last * kTileJ, self_slot0);
+        if (a.mask_self && jt_last >= diag0 && jt_last < diag0 + I)
+            tile_interact<I, true, kLoop, false>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, 0, tq1, jt_last * kTileJ, self_slot0);
+        else
+            tile_interact<I, false, kLoop, false>(sA[buf], sB[buf], xi, yi, zi, eps2, ax, ay, az, 0, tq1, jt_last * kTileJ, self_slot0);
         __syncthreads();                                 // the next segment restages buffer 0
     }
 #pragma unroll
