@@ -388,14 +388,14 @@ def run_ours(args):
         pinned = nb.PinnedParticles(cnt)
         pinned.array[:] = local
         for s in range(min(2, args.warmup)):
-            sim.computeStep(pinned.array, params)
+            sim.computeStep(pinned.array, params, n_total=n)
         barrier()
         t0 = time.perf_counter()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with torch.cuda.stream(ext):
             e0.record(ext)
         for s in range(args.steps):
-            sim.computeStep(pinned.array, params)     # H2D of the slice, step (+exchange), D2H of the slice
+            sim.computeStep(pinned.array, params, n_total=n)     # H2D of the slice, step (+exchange), D2H of the slice
         with torch.cuda.stream(ext):
             e1.record(ext)
         barrier()
@@ -409,7 +409,7 @@ def run_ours(args):
         e2e = {"value": float(n) * n * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(cnt * 40), "d2h_bytes_per_step": int(cnt * 40),
                "ms_per_step": ms_e2e / args.steps, "host_wall_ms_per_step": wall / args.steps * 1e3,
-               "call": "CudaNaiveSimulation.computeStep(pinned host slice) -> nbody_cuda_upload_aos/_step/_download_aos"}
+               "call": "CudaNaiveSimulation.computeStep(pinned host slice, params, n_total) -> nbody_cuda_upload_aos/[_exchange]/_step/_download_aos"}
         pinned.close()
 
     # ---- roofline of the dominant kernel (force accumulation) ----

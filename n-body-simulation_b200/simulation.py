@@ -272,8 +272,12 @@ class CudaNaiveSimulation:
         self._ck(self._lib.nbody_cuda_synchronize(self._h))
 
     # -- the reference interface ------------------------------------------------------------
-    def computeStep(self, particles: np.ndarray, params: SimParams) -> None:
+    def computeStep(self, particles: np.ndarray, params: SimParams, n_total: int | None = None) -> None:
         """One step in place; the host array is the source of truth on entry and on return.
+
+        With a group, `n_total` (the global particle count, the same on every rank) saves the count
+        all-reduce that otherwise precedes every call -- the reference re-gathers the counts each step too
+        (src/MpiNaiveSimulation.cpp:33-35); a caller whose slices never change size can state the total once.
 
         Single GPU: NaiveSimulation::computeStep (src/NaiveSimulation.cpp:7-10).
         With a group: MpiNaiveSimulation::computeStep on this rank's slice
@@ -284,7 +288,7 @@ class CudaNaiveSimulation:
                 self._h, p.ctypes.data_as(C.c_void_p), p.shape[0], params.G, params.dt, params.min_r2))
             self.n_total = p.shape[0]
             return
-        self.upload(p)
+        self.upload(p, n_total=n_total)
         self.step(params, 1)
         self.download(p)
 
