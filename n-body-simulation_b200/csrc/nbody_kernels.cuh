@@ -174,23 +174,18 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
 #pragma unroll
         for (int k = 0; k < I; ++k) {
             const u64 dx = sub2(xj, xi[k]), dy = sub2(yj, yi[k]), dz = sub2(zj, zi[k]);
-            // The order in which the three squares and the three accumulations are written changes nothing
-            // arithmetically worth mentioning, but it changes ptxas's schedule, and the schedules differ by up to
-            // 4 % on the hardware (MUFU results consumed too early at the loop end).  Each loop uses the order that
-            // measured fastest in a 68-variant sweep on B200 (gpurun_out/r2k_matrix.log, r2l_matrix.log).
-            u64 r2;
-            if (kLoop == kLoopMassMul) {
-                r2 = fma2(dy, dy, eps2);
-                r2 = fma2(dx, dx, r2);
-                r2 = fma2(dz, dz, r2);
-            } else {
-                r2 = fma2(dx, dx, eps2);
-                r2 = fma2(dy, dy, r2);
-                r2 = fma2(dz, dz, r2);
-            }
+            // How this body is written (order of the squares, of the accumulations and their operands, which lane's
+            // MUFU comes first) changes nothing arithmetically worth mentioning, but it changes ptxas's schedule, and
+            // the schedules differ by up to 4 % on the hardware (MUFU results consumed too early at the loop end).
+            // This is the form that measured fastest for BOTH loops in an 85-variant sweep on B200
+            // (profiles/r2_kernel_variant_matrix.md).
+            u64 r2 = fma2(dx, dx, eps2);
+            r2 = fma2(dy, dy, r2);
+            r2 = fma2(dz, dz, r2);
             float r2lo, r2hi;
             unpack2(r2, r2lo, r2hi);
-            const u64 rinv = pack2(rsqrt_approx(r2lo), rsqrt_approx(r2hi));
+            const float rhi = rsqrt_approx(r2hi), rlo = rsqrt_approx(r2lo);      // high lane first
+            const u64 rinv = pack2(rlo, rhi);
             const u64 rinv2 = mul2(rinv, rinv);
             u64 s = (kLoop == kLoopMassMul) ? mul2(mul2(mj, rinv2), rinv) : mul2(rinv2, rinv);   // [m_j] / r^3
             if (kMaskSelf) {                       // the reference skips j == i by index
@@ -201,15 +196,9 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
                 shi = (j0 + 1 == self) ? 0.0f : shi;
                 s = pack2(slo, shi);
             }
-            if (kLoop == kLoopMassMul) {
-                az[k] = fma2(dz, s, az[k]);
-                ay[k] = fma2(dy, s, ay[k]);
-                ax[k] = fma2(dx, s, ax[k]);
-            } else {
-                ax[k] = fma2(s, dx, ax[k]);
-                ay[k] = fma2(s, dy, ay[k]);
-                az[k] = fma2(s, dz, az[k]);
-            }
+            ax[k] = fma2(s, dx, ax[k]);
+            ay[k] = fma2(s, dy, ay[k]);
+            az[k] = fma2(s, dz, az[k]);
         }
     }
 }
