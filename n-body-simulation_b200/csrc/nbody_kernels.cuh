@@ -177,7 +177,7 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
             // How this body is written (order of the squares, of the accumulations and their operands, which lane's
             // MUFU comes first) changes nothing arithmetically worth mentioning, but it changes ptxas's schedule, and
             // the schedules differ by up to 4 % on the hardware (MUFU results consumed too early at the loop end).
-            // This is the form that measured fastest for BOTH loops in an 85-variant sweep on B200
+            // This is the form that measured fastest for BOTH loops in a 93-variant sweep on B200
             // (profiles/r2_kernel_variant_matrix.md).
             u64 r2 = fma2(dx, dx, eps2);
             r2 = fma2(dy, dy, r2);
@@ -187,7 +187,7 @@ __device__ __forceinline__ void tile_interact(const float4 *__restrict__ sA, con
             const float rhi = rsqrt_approx(r2hi), rlo = rsqrt_approx(r2lo);      // high lane first
             const u64 rinv = pack2(rlo, rhi);
             const u64 rinv2 = mul2(rinv, rinv);
-            u64 s = (kLoop == kLoopMassMul) ? mul2(mul2(mj, rinv2), rinv) : mul2(rinv2, rinv);   // [m_j] / r^3
+            u64 s = (kLoop == kLoopMassMul) ? mul2(rinv, mul2(mj, rinv2)) : mul2(rinv, rinv2);   // [m_j] / r^3
             if (kMaskSelf) {                       // the reference skips j == i by index
                 float slo, shi;
                 unpack2(s, slo, shi);
