@@ -4,7 +4,7 @@ cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 ncu --query-metrics > gpurun_out/r2_ncu_query_metrics.txt 2>&1
 EXTRA="smsp__inst_executed.sum,smsp__inst_issued.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active,sm__inst_executed_pipe_fma.sum,sm__inst_executed_pipe_xu.sum,sm__inst_executed_pipe_alu.sum,sm__inst_executed_pipe_lsu.sum,sm__inst_executed_pipe_uniform.sum"
-for c in "262144 plummer" "262144 disk" "1048576 disk" "20000 plummer" "20000 disk"; do
+for c in "262144 plummer" "262144 disk" "1048576 plummer" "1048576 disk" "20000 plummer" "20000 disk"; do
   tag=$(echo $c | tr ' ' '_')
   python tools/ncu_case.py $c > gpurun_out/r2_ncu_plain_$tag.log 2>&1 &&
   ncu --set full --metrics $EXTRA --clock-control none --import-source on -k regex:force_fast_kernel -s 2 -c 1 -o gpurun_out/r2_prof_$tag -f python tools/ncu_case.py $c > gpurun_out/r2_ncu_full_$tag.log 2>&1
